@@ -1,0 +1,112 @@
+// Shared host-side declarations for the fangyan_b200 library (context, errors, kernel launch protos).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/fangyan_b200.h"
+
+namespace fy {
+
+// ---------------------------------------------------------------- errors
+void set_error(const char* fmt, ...);
+#define FY_CHECK(cond, code, ...)  \
+  do {                             \
+    if (!(cond)) {                 \
+      fy::set_error(__VA_ARGS__);  \
+      return (code);               \
+    }                              \
+  } while (0)
+#define FY_CUDA(expr)                                                                    \
+  do {                                                                                   \
+    cudaError_t _e = (expr);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      fy::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return FY_ERR_CUDA;                                                                \
+    }                                                                                    \
+  } while (0)
+#define FY_TRY(expr)             \
+  do {                           \
+    int _r = (expr);             \
+    if (_r != FY_OK) return _r;  \
+  } while (0)
+
+// ---------------------------------------------------------------- GEMM
+constexpr int kMaxSeg = 32;
+struct GemmSeg {
+  int a_row_off;  // added to the tile's first row for the A load (may be negative: TMA zero-fills)
+  int a_col;      // first K column in A
+  int b_col;      // first K column in B
+  int nkb;        // number of 64-wide K blocks
+};
+
+enum EpiMode { EPI_BF16 = 0, EPI_F32_ADD = 1, EPI_F32_STORE = 2 };
+enum EpiAct { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
+
+struct GemmEpi {
+  int mode = EPI_BF16;
+  int act = ACT_NONE;
+  void* out = nullptr;   // bf16 or float
+  int ldo = 0;           // leading dimension of out (elements)
+  int col_off = 0;       // column offset of this GEMM's N range inside out
+  int lo_col_off = -1;   // EPI_BF16 only: if >= 0 also write the bf16 residual (x - bf16(x)) at this column offset
+  const float* scale = nullptr;    // [N] per-column multiplier (folded BatchNorm) or null
+  const float* bias = nullptr;     // [N] per-column addend or null
+  const int* row_idx = nullptr;    // [M] or null: rows with row_idx < 0 are written as zero
+  const float* row_gate = nullptr; // [*, N] or null: multiply by row_gate[row_idx[row] * N + n] (CAM mask)
+};
+
+struct GemmArgs {
+  CUtensorMap tmap_a;
+  CUtensorMap tmap_b;
+  int M = 0, N = 0;
+  int nseg = 0;
+  GemmSeg seg[kMaxSeg];
+  GemmEpi epi;
+};
+
+// Encode a 2-D bf16 row-major [rows, cols] tensor map (ld in elements) with a {64, box_rows} box, 128B swizzle.
+int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows);
+int gemm_block_n(int N);  // tile width the launcher picks for this N (32, 128 or 256)
+int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st);
+
+// ---------------------------------------------------------------- context
+struct Tensor {
+  void* ptr = nullptr;   // device
+  size_t bytes = 0;
+  std::vector<int64_t> shape;
+};
+
+struct Ctx {
+  int device = 0;
+  int num_sms = 148;
+  int precision = FY_PREC_BF16X3;
+  cudaStream_t stream = nullptr;
+  // front-end tables (device)
+  float* fb_window = nullptr;      // [400] povey
+  float* fb_mel_w = nullptr;       // packed mel weights
+  int* fb_mel_off = nullptr;       // [80] first fft bin
+  int* fb_mel_len = nullptr;       // [80]
+  int* fb_mel_ptr = nullptr;       // [80] offset into fb_mel_w
+  float2* fb_tw = nullptr;         // [256] twiddles for N=512
+  float* wh_window = nullptr;      // [400] hann periodic
+  float* wh_mel_w = nullptr;
+  int* wh_mel_off = nullptr;
+  int* wh_mel_len = nullptr;
+  int* wh_mel_ptr = nullptr;
+  float2* wh_tw = nullptr;         // [400] twiddles for N=400
+  // model weights (device, owned)
+  std::map<std::string, Tensor> cam_w;
+  std::map<std::string, Tensor> s3_w;
+  void* cam_plan = nullptr;
+  void* s3_plan = nullptr;
+  std::map<std::pair<int, int>, float*> resample_kern;  // (orig, new) reduced -> device filter bank
+  std::vector<void*> owned;        // misc device allocations freed in destroy
+};
+
+}  // namespace fy

@@ -1,0 +1,319 @@
+// Persistent warp-specialised bf16 GEMM for sm_100a: TMA -> shared (128B swizzle) -> tcgen05.mma -> TMEM
+// -> tcgen05.ld epilogue.   D[M,N] = sum_s A_s[M,K_s] * B_s[N,K_s]^T, fp32 accumulate.
+//
+// "Segments" let one launch accumulate several (row-shifted A view, B column range) products into the
+// same TMEM accumulator.  That one mechanism expresses
+//   * the 3-term split-bf16 product (hi*hi + hi*lo + lo*hi) used for fp32-faithful results,
+//   * 1-D convolutions over time-major activations (one segment per tap, row offset = tap * dilation),
+//   * strided convolutions through a "two rows per row" view of the input.
+// Rows outside the tensor (negative or past the end) are zero-filled by TMA, which is the convolution's
+// zero padding.
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "fy_common.cuh"
+#include "fy_ptx.cuh"
+
+namespace fy {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kThreads = 256;
+constexpr int kEpiThreads = 128;
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+  // tiles + barriers + scale/bias staging + alignment slack
+  static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 2 * BN * 4 + 1024;
+};
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmArgs args) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tiles = smem;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* tfull_bar = empty_bar + C::kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  float* s_scale = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);
+  float* s_bias = s_scale + BN;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int num_m = (args.M + BM - 1) / BM;
+  const int num_n = args.N / BN;
+  const int num_tiles = num_m * num_n;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&args.tmap_a);
+    ptx::prefetch_tmap(&args.tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < C::kStages; ++i) {
+      ptx::mbar_init(&full_bar[i], 1);
+      ptx::mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tfull_bar[i], 1);
+      ptx::mbar_init(&tempty_bar[i], kEpiThreads);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<C::kTmemCols>(tmem_holder);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / num_n) * BM;
+        const int n0 = (tile % num_n) * BN;
+        for (int s = 0; s < args.nseg; ++s) {
+          const GemmSeg sg = args.seg[s];
+          for (int kb = 0; kb < sg.nkb; ++kb) {
+            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* a_dst = tiles + stage * C::kStageBytes;
+            uint8_t* b_dst = a_dst + C::kABytes;
+            ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes);
+            ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BK, m0 + sg.a_row_off);
+            ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BK, n0);
+            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        uint32_t accumulate = 0;
+        for (int s = 0; s < args.nseg; ++s) {
+          const int nkb = args.seg[s].nkb;
+          for (int kb = 0; kb < nkb; ++kb) {
+            ptx::mbar_wait(&full_bar[stage], phase);
+            ptx::tc_fence_after();
+            const uint32_t a_addr = ptx::smem_u32(tiles + stage * C::kStageBytes);
+            const uint64_t da = ptx::make_desc_sw128(a_addr);
+            const uint64_t db = ptx::make_desc_sw128(a_addr + C::kABytes);
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              ptx::mma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              accumulate = 1;
+            }
+            ptx::mma_commit(&empty_bar[stage]);
+            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+        ptx::mma_commit(&tfull_bar[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (warps 4..7 = TMEM lane quarters 0..3) =====================
+    const int q = warp - 4;
+    const int et = threadIdx.x - 128;
+    const GemmEpi& e = args.epi;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile / num_n) * BM;
+      const int n0 = (tile % num_n) * BN;
+      asm volatile("bar.sync 1, 128;\n" ::: "memory");
+      for (int i = et; i < BN; i += kEpiThreads) {
+        s_scale[i] = e.scale ? __ldg(e.scale + n0 + i) : 1.0f;
+        s_bias[i] = e.bias ? __ldg(e.bias + n0 + i) : 0.0f;
+      }
+      asm volatile("bar.sync 1, 128;\n" ::: "memory");
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < args.M;
+      int ridx = 0;
+      if (e.row_idx) ridx = row_ok ? __ldg(e.row_idx + row) : -1;
+      const bool keep = ridx >= 0;
+      ptx::mbar_wait(&tfull_bar[as], aphase);
+      ptx::tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(t_row + c * 32, v);
+        ptx::tmem_ld_wait();
+        if (row_ok) {
+          float x[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float t = __uint_as_float(v[j]) * s_scale[c * 32 + j] + s_bias[c * 32 + j];
+            if (e.act == ACT_GELU) t = gelu_erf(t);
+            else if (e.act == ACT_RELU) t = fmaxf(t, 0.0f);
+            x[j] = t;
+          }
+          if (e.row_gate && keep) {
+            const float4* g = reinterpret_cast<const float4*>(e.row_gate + (size_t)ridx * args.N + n0 + c * 32);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float4 gv = __ldg(g + j);
+              x[4 * j] *= gv.x; x[4 * j + 1] *= gv.y; x[4 * j + 2] *= gv.z; x[4 * j + 3] *= gv.w;
+            }
+          }
+          if (!keep) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = 0.0f;
+          }
+          const size_t col = (size_t)e.col_off + n0 + c * 32;
+          if (e.mode == EPI_BF16) {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + (size_t)row * e.ldo;
+            uint4* dst = reinterpret_cast<uint4*>(o + col);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 w;
+              w.x = pack_bf16(x[8 * j], x[8 * j + 1]);
+              w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
+              w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]);
+              w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+              dst[j] = w;
+            }
+            if (e.lo_col_off >= 0) {
+              uint4* dlo = reinterpret_cast<uint4*>(o + (size_t)e.lo_col_off + n0 + c * 32);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) x[j] -= __bfloat162float(__float2bfloat16_rn(x[j]));
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                uint4 w;
+                w.x = pack_bf16(x[8 * j], x[8 * j + 1]);
+                w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
+                w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]);
+                w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+                dlo[j] = w;
+              }
+            }
+          } else {
+            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + (size_t)row * e.ldo + col);
+            if (e.mode == EPI_F32_ADD) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float4 r = dst[j];
+                r.x += x[4 * j]; r.y += x[4 * j + 1]; r.z += x[4 * j + 2]; r.w += x[4 * j + 3];
+                dst[j] = r;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) dst[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&tempty_bar[as]);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+template <int BN>
+int launch_bn(const GemmArgs& a, int num_sms, cudaStream_t st) {
+  using C = Cfg<BN>;
+  static bool configured = false;
+  if (!configured) {
+    FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    configured = true;
+  }
+  const int tiles = ((a.M + BM - 1) / BM) * (a.N / BN);
+  const int grid = tiles < num_sms ? tiles : num_sms;
+  gemm_kernel<BN><<<grid, kThreads, C::kSmemBytes, st>>>(a);
+  FY_CUDA(cudaGetLastError());
+  return FY_OK;
+}
+
+}  // namespace
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  FY_CHECK(enc != nullptr, FY_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  FY_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0, FY_ERR_ARG,
+           "tensor map base/stride must be 16-byte aligned (ld=%llu)", (unsigned long long)ld);
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  FY_CHECK(r == CUDA_SUCCESS, FY_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d (rows=%llu cols=%llu ld=%llu)", (int)r,
+           (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld);
+  return FY_OK;
+}
+
+int gemm_block_n(int N) {
+  if (N % 256 == 0) return 256;
+  if (N % 128 == 0) return 128;
+  if (N % 32 == 0) return 32;
+  return 0;
+}
+
+int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st) {
+  FY_CHECK(a.M > 0 && a.nseg > 0 && a.nseg <= kMaxSeg, FY_ERR_ARG, "bad GEMM shape M=%d nseg=%d", a.M, a.nseg);
+  FY_CHECK(a.epi.out != nullptr && a.epi.ldo > 0, FY_ERR_ARG, "GEMM epilogue has no output");
+  switch (gemm_block_n(a.N)) {
+    case 256: return launch_bn<256>(a, num_sms, st);
+    case 128: return launch_bn<128>(a, num_sms, st);
+    case 32: return launch_bn<32>(a, num_sms, st);
+    default: FY_CHECK(false, FY_ERR_ARG, "GEMM N=%d must be a multiple of 32", a.N);
+  }
+  return FY_OK;
+}
+
+}  // namespace fy

@@ -1,0 +1,127 @@
+/* fangyan_b200 -- C ABI of the B200-native stage 1+2 extraction path.
+ *
+ * The reference (Autonomof/fangyan-TTS) has no FFI for this path: its boundary is two Python CLIs that call
+ * torchaudio / openai-whisper for the front-ends and onnxruntime InferenceSession.run() for the two networks.
+ * Every entry point below cites the reference call it replaces (paths relative to /root/reference/CosyVoice).
+ *
+ * Conventions
+ *   - every function returns FY_OK (0) or a negative fy_status; fy_last_error() gives a thread-local message.
+ *   - all data pointers are DEVICE pointers unless the parameter name starts with h_ (host).
+ *   - utterances are passed PACKED: one contiguous array plus an int32 offsets array of n_utts + 1 entries
+ *     (exclusive prefix sums), never padded.  The reference runs every utterance alone at its true length
+ *     (tools/extract_embedding.py:25-42), so there is no padding to reproduce.
+ *   - launches are asynchronous on the context's stream (fy_set_stream); nothing here synchronises.
+ *   - the caller owns inputs, outputs and the workspace; the library owns weights and lookup tables.
+ *   - a fy_ctx is not thread-safe: one per worker / GPU.
+ */
+#ifndef FANGYAN_B200_H_
+#define FANGYAN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fy_ctx fy_ctx;
+
+typedef enum {
+  FY_OK = 0,
+  FY_ERR_ARG = -1,     /* bad argument / shape / alignment (checked on the host before any launch) */
+  FY_ERR_CUDA = -2,    /* a CUDA runtime or driver call failed */
+  FY_ERR_STATE = -3,   /* weights not loaded, wrong device, ... */
+  FY_ERR_NOMEM = -4    /* workspace too small */
+} fy_status;
+
+typedef enum {
+  FY_PREC_BF16 = 0,    /* single bf16 tensor-core pass, fp32 accumulate */
+  FY_PREC_BF16X3 = 1   /* split-bf16 (hi*hi + hi*lo + lo*hi), fp32-faithful: the parity mode and the default */
+} fy_precision;
+
+typedef enum { FY_PCM_S16 = 0, FY_PCM_F32 = 1 } fy_pcm_dtype;
+
+/* One named fp32 weight tensor on the HOST (an ONNX initialiser or a state-dict entry). */
+typedef struct {
+  const char* name;
+  const float* h_data;
+  int32_t ndim;
+  int64_t shape[4];
+} fy_tensor;
+
+/* Hyper-parameters of the S3 tokenizer encoder (UNVERIFIED against the real ONNX graph). */
+typedef struct {
+  int32_t n_mels, d_model, n_head, n_layer, d_ff, fsmn_kernel, fsq_dim;
+  float rope_theta, ln_eps, fsq_scale;
+} fy_s3_config;
+
+/* ---- lifetime ------------------------------------------------------------------------------------------- */
+int fy_create(int device, int precision, fy_ctx** out);
+void fy_destroy(fy_ctx* ctx);
+const char* fy_last_error(void);
+int fy_set_stream(fy_ctx* ctx, void* cuda_stream);
+const char* fy_version(void);
+
+/* ---- weights: replaces onnxruntime.InferenceSession(onnx_path) ---------------------------------------------
+ * tools/extract_embedding.py:94, tools/extract_speech_token.py:90, cosyvoice/cli/frontend.py:45-48.
+ * BatchNorm folding, bf16 hi/lo splitting and conv-weight re-layout happen here, once. */
+int fy_load_campplus(fy_ctx* ctx, const fy_tensor* h_tensors, int n);
+int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* h_tensors, int n, const fy_s3_config* cfg);
+
+/* ---- A2: torchaudio.transforms.Resample(orig, 16000) ------------------------------------------------------
+ * tools/extract_embedding.py:27-28, tools/extract_speech_token.py:29-30, cosyvoice/utils/file_utils.py:47-49.
+ * One launch resamples a packed batch that shares one input rate.  Output length per utterance is
+ * ceil(new * n_in / orig) (after dividing both rates by their gcd); out_off must hold those prefix sums and
+ * total_out is their last entry (host value). */
+int fy_resample(fy_ctx* ctx, const float* in, const int32_t* in_off, float* out, const int32_t* out_off, int n_utts,
+                int total_out, int orig_freq, int new_freq);
+
+/* ---- A3 + A4: kaldi.fbank(num_mel_bins=80, dither=0, sample_frequency=16000) then feat - feat.mean(0) ------
+ * tools/extract_embedding.py:29-33, cosyvoice/cli/frontend.py:110-114.
+ * pcm: packed mono samples (int16, scaled by 1/32768 on the device -- row A1 -- or float32).
+ * feat: packed [sum M_b, 80] fp32, M_b = 1 + (N_b - 400) / 160 (0 when N_b < 400); frame_off = prefix sums of M_b.
+ * ws: at least fy_fbank_workspace_bytes(n_utts, total_frames) bytes. */
+size_t fy_fbank_workspace_bytes(int n_utts, int total_frames);
+int fy_fbank_cmn(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
+                 int n_utts, int total_frames, float* feat, void* ws, size_t ws_bytes);
+
+/* ---- A5: whisper.log_mel_spectrogram(audio, n_mels=128) ---------------------------------------------------
+ * tools/extract_speech_token.py:38, cosyvoice/cli/frontend.py:98.
+ * mel: packed; utterance b occupies 128 * T_b floats starting at 128 * frame_off[b], laid out [128][T_b] exactly
+ * like the reference's [1, 128, T] tensor.  T_b = N_b / 160.  max_frames = largest T_b in the batch (host value). */
+size_t fy_logmel_workspace_bytes(int n_utts, int total_frames);
+int fy_logmel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
+              int n_utts, int total_frames, int max_frames, float* mel, void* ws, size_t ws_bytes);
+
+/* ---- A6: ort_session.run(None, {"input": feat[None]}) on campplus.onnx ------------------------------------
+ * tools/extract_embedding.py:36-41, cosyvoice/cli/frontend.py:115-116.
+ * feat: packed [sum M_b, 80] fp32 (output of fy_fbank_cmn); emb: [n_utts, 192] fp32. */
+size_t fy_campplus_workspace_bytes(fy_ctx* ctx, int n_utts, int total_frames);
+int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t* frame_off, const int32_t* h_frame_off,
+                        int n_utts, float* emb, void* ws, size_t ws_bytes);
+
+/* ---- A9 + A10: ort_session.run(None, {feat, feat_len}) on speech_tokenizer_v3.onnx ------------------------
+ * tools/extract_speech_token.py:40-48, cosyvoice/cli/frontend.py:99-103.
+ * mel: packed as written by fy_logmel.  tokens: packed int32, L_b = ((T_b - 1) / 2 + 1 - 1) / 2 + 1 per utterance;
+ * tok_off = prefix sums of L_b.  h_frame_off is the host copy of frame_off (needed to plan the launch).
+ * fsq_pre (optional, may be NULL): packed [sum L_b, 8] fp32 pre-rounding values, for boundary-distance checks. */
+size_t fy_s3tok_workspace_bytes(fy_ctx* ctx, int n_utts, int total_frames);
+int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off, const int32_t* h_frame_off,
+                        int n_utts, int32_t* tokens, const int32_t* tok_off, float* fsq_pre, void* ws,
+                        size_t ws_bytes);
+
+/* ---- A7: per-speaker mean of utterance embeddings (tools/extract_embedding.py:50-56) ----------------------
+ * spk_id[b] in [0, n_spk).  sum: [n_spk, 192] fp32 and count: [n_spk] int32 are ACCUMULATED into (zero them first),
+ * so partial sums from several batches / ranks can be combined (all_reduce SUM) before fy_speaker_mean_finish. */
+int fy_speaker_sum(fy_ctx* ctx, const float* emb, const int32_t* spk_id, int n_utts, int n_spk, float* sum,
+                   int32_t* count);
+int fy_speaker_mean_finish(fy_ctx* ctx, const float* sum, const int32_t* count, int n_spk, float* mean);
+
+/* ---- generic bf16 tensor-core GEMM (exposed for tests and tuning) -----------------------------------------
+ * out[M, N] (fp32) = A[M, K] * B[N, K]^T with A, B bf16 row-major. */
+int fy_gemm_bf16(fy_ctx* ctx, const void* a_bf16, const void* b_bf16, float* out, int M, int N, int K);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FANGYAN_B200_H_ */
