@@ -1,0 +1,210 @@
+// Row-wise kernels of the S3 tokenizer encoder (rows A9/A10): layout change, LayerNorm, RoPE + split, FSMN memory,
+// FSQ.  All HBM-bound; activations are fp32 in the residual stream and bf16 (hi | lo) as tensor-core operands.
+#pragma once
+#include "fy_common.cuh"
+
+namespace fy {
+namespace s3k {
+
+__device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(x);
+  lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// mel (reference layout [128][T_u] per utterance, fp32) -> time-major bf16 rows at row 4*P_u + 3 + t.
+// rows: [Rmel, 128 * W] with hi at [0,128) and (W == 2) lo at [128,256).  Buffer is zeroed beforehand.
+// grid: (ceil(Tmax / 32), n_utts), block 256.
+template <bool SPLIT>
+__global__ void __launch_bounds__(256) mel_to_rows_kernel(const float* __restrict__ mel,
+                                                          const int* __restrict__ frame_off,
+                                                          const int* __restrict__ utt_P, __nv_bfloat16* __restrict__ rows) {
+  __shared__ float tile[128][33];
+  const int u = blockIdx.y;
+  const int t0 = blockIdx.x * 32;
+  const int f0 = frame_off[u];
+  const int T = frame_off[u + 1] - f0;
+  if (t0 >= T) return;
+  const float* src = mel + (size_t)f0 * 128;
+  for (int i = threadIdx.x; i < 128 * 32; i += 256) {
+    const int b = i >> 5, t = i & 31;
+    tile[b][t] = (t0 + t < T) ? src[(size_t)b * T + t0 + t] : 0.f;
+  }
+  __syncthreads();
+  constexpr int LD = SPLIT ? 256 : 128;
+  const size_t row0 = (size_t)4 * utt_P[u] + 3 + t0;
+  for (int i = threadIdx.x; i < 32 * 128; i += 256) {
+    const int t = i >> 7, b = i & 127;
+    if (t0 + t < T) {
+      __nv_bfloat16 hi, lo;
+      split_bf16(tile[b][t], hi, lo);
+      rows[(row0 + t) * LD + b] = hi;
+      if (SPLIT) rows[(row0 + t) * LD + 128 + b] = lo;
+    }
+  }
+}
+
+// LayerNorm over D (multiple of 128) per row: one warp per row.  out bf16 [rows, D * W] (hi | lo).
+template <bool SPLIT, int D>
+__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, float eps, int rows,
+                                                        __nv_bfloat16* __restrict__ out) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  constexpr int NV = D / 128;  // float4 per lane
+  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * D);
+  float4 v[NV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    v[i] = xr[lane + 32 * i];
+    s += v[i].x + v[i].y + v[i].z + v[i].w;
+  }
+  const float mean = warp_sum(s) * (1.0f / D);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+    q += a * a + b * b + c * c + d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.0f / D) + eps);
+  constexpr int LD = SPLIT ? 2 * D : D;
+  __nv_bfloat16* o = out + (size_t)row * LD;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (lane + 32 * i) * 4;
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(beta + c));
+    float y[4] = {(v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y,
+                  (v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w};
+    __nv_bfloat16 hi[4], lo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) split_bf16(y[j], hi[j], lo[j]);
+    *reinterpret_cast<uint2*>(o + c) = *reinterpret_cast<uint2*>(hi);
+    if (SPLIT) *reinterpret_cast<uint2*>(o + D + c) = *reinterpret_cast<uint2*>(lo);
+  }
+}
+
+// qkv fp32 [rows, 3D] -> q, k (RoPE, rotate-half, then * scale) and v as bf16 [rows, D * W] (hi | lo).
+// One thread per (row, head, d < DH/2) handles the pair (d, d + DH/2) of q and k and two v values.
+template <bool SPLIT>
+__global__ void __launch_bounds__(256) rope_split_kernel(const float* __restrict__ qkv, const int* __restrict__ row_pos,
+                                                         const float* __restrict__ cosT, const float* __restrict__ sinT,
+                                                         int rows, int D, int DH, float scale,
+                                                         __nv_bfloat16* __restrict__ q, __nv_bfloat16* __restrict__ k,
+                                                         __nv_bfloat16* __restrict__ v) {
+  const int half = DH / 2;
+  const int per_row = D / 2;
+  const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (size_t)rows * per_row) return;
+  const int row = (int)(idx / per_row);
+  const int r = (int)(idx % per_row);
+  const int h = r / half, d = r % half;
+  const int c0 = h * DH + d, c1 = c0 + half;
+  int pos = __ldg(row_pos + row);
+  if (pos < 0) pos = 0;
+  const float cs0 = __ldg(cosT + (size_t)pos * DH + d), sn0 = __ldg(sinT + (size_t)pos * DH + d);
+  const float cs1 = __ldg(cosT + (size_t)pos * DH + d + half), sn1 = __ldg(sinT + (size_t)pos * DH + d + half);
+  const float* src = qkv + (size_t)row * 3 * D;
+  const int LD = SPLIT ? 2 * D : D;
+  const size_t o = (size_t)row * LD;
+  __nv_bfloat16 hi, lo;
+  {
+    const float a = src[c0], b = src[c1];
+    split_bf16((a * cs0 - b * sn0) * scale, hi, lo);
+    q[o + c0] = hi; if (SPLIT) q[o + D + c0] = lo;
+    split_bf16((b * cs1 + a * sn1) * scale, hi, lo);
+    q[o + c1] = hi; if (SPLIT) q[o + D + c1] = lo;
+  }
+  {
+    const float a = src[D + c0], b = src[D + c1];
+    split_bf16((a * cs0 - b * sn0) * scale, hi, lo);
+    k[o + c0] = hi; if (SPLIT) k[o + D + c0] = lo;
+    split_bf16((b * cs1 + a * sn1) * scale, hi, lo);
+    k[o + c1] = hi; if (SPLIT) k[o + D + c1] = lo;
+  }
+  {
+    split_bf16(src[2 * D + c0], hi, lo);
+    v[o + c0] = hi; if (SPLIT) v[o + D + c0] = lo;
+    split_bf16(src[2 * D + c1], hi, lo);
+    v[o + c1] = hi; if (SPLIT) v[o + D + c1] = lo;
+  }
+}
+
+// FSMN memory: x[row, c] += v[row, c] + sum_j w[c][j] * v[row + j - pad, c] over rows of the same utterance.
+// v is the fp32 value projection inside qkv (column offset 2D).  One thread per (row, 4 channels).
+__global__ void __launch_bounds__(256) fsmn_kernel(const float* __restrict__ qkv, const int* __restrict__ row_utt,
+                                                   const int* __restrict__ row_pos, const int* __restrict__ utt_L,
+                                                   const float* __restrict__ w /* [KS][D] tap-major */, int rows, int D,
+                                                   int KS, float* __restrict__ x) {
+  const int per_row = D / 4;
+  const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (size_t)rows * per_row) return;
+  const int row = (int)(idx / per_row);
+  const int c = (int)(idx % per_row) * 4;
+  const int u = __ldg(row_utt + row);
+  if (u < 0) return;
+  const int pos = __ldg(row_pos + row);
+  const int L = __ldg(utt_L + u);
+  const int pad = (KS - 1) / 2;
+  const size_t ldv = (size_t)3 * D;
+  const float* vbase = qkv + 2 * D + c;
+  float4 acc = *reinterpret_cast<const float4*>(vbase + (size_t)row * ldv);
+  const int j0 = max(0, pad - pos), j1 = min(KS, L - pos + pad);
+  for (int j = j0; j < j1; ++j) {
+    const float4 vv = *reinterpret_cast<const float4*>(vbase + (size_t)(row + j - pad) * ldv);
+    const float4 ww = __ldg(reinterpret_cast<const float4*>(w + (size_t)j * D + c));
+    acc.x += ww.x * vv.x; acc.y += ww.y * vv.y; acc.z += ww.z * vv.z; acc.w += ww.w * vv.w;
+  }
+  float4* xp = reinterpret_cast<float4*>(x + (size_t)row * D + c);
+  float4 xv = *xp;
+  xv.x += acc.x; xv.y += acc.y; xv.z += acc.z; xv.w += acc.w;
+  *xp = xv;
+}
+
+// FSQ: z = W[8, D] x + b -> tanh -> * scale -> pre; id = sum (rint(pre) + 1) * 3^i.  One warp per token row;
+// output index = tok_off[u] + pos.
+__global__ void __launch_bounds__(256) fsq_kernel(const float* __restrict__ x, const int* __restrict__ row_utt,
+                                                  const int* __restrict__ row_pos, const int* __restrict__ tok_off,
+                                                  const float* __restrict__ w, const float* __restrict__ b, int rows,
+                                                  int D, float fsq_scale, int* __restrict__ tokens,
+                                                  float* __restrict__ pre_out) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int u = __ldg(row_utt + row);
+  if (u < 0) return;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const float* xr = x + (size_t)row * D;
+  for (int c = lane * 4; c < D; c += 128) {
+    const float4 xv = *reinterpret_cast<const float4*>(xr + c);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 wv = __ldg(reinterpret_cast<const float4*>(w + (size_t)i * D + c));
+      acc[i] += xv.x * wv.x + xv.y * wv.y + xv.z * wv.z + xv.w * wv.w;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = warp_sum(acc[i]);
+  if (lane == 0) {
+    const size_t o = (size_t)__ldg(tok_off + u) + __ldg(row_pos + row);
+    int id = 0, p3 = 1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float pre = tanhf(acc[i] + __ldg(b + i)) * fsq_scale;
+      if (pre_out) pre_out[o * 8 + i] = pre;
+      id += ((int)rintf(pre) + 1) * p3;
+      p3 *= 3;
+    }
+    tokens[o] = id;
+  }
+}
+
+}  // namespace s3k
+}  // namespace fy

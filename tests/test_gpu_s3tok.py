@@ -1,0 +1,68 @@
+"""GPU parity: S3 tokenizer encoder + FSQ through the C ABI vs the CPU oracle (oracle/s3tokenizer.py)."""
+import numpy as np
+import pytest
+import torch
+
+from fangyan_tts_b200 import synth
+from fangyan_tts_b200.engine import Engine
+from oracle import frontend as F
+from oracle import s3tokenizer as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _state(model, cfg, n=2048):
+    st = dict(model.state_dict())
+    cos, sin = S.rope_tables(n, cfg.d_head, cfg.rope_theta)
+    st["rope.cos"], st["rope.sin"] = cos, sin
+    return st
+
+
+def _mels(utts):
+    return [F.whisper_log_mel(torch.from_numpy(u.astype(np.float32) / 32768.0)[None]) for u in utts]
+
+
+def _run(eng, model, mels):
+    frames = [m.shape[2] for m in mels]
+    packed = torch.cat([m[0].reshape(-1) for m in mels]).cuda()
+    tok, lens, pre = eng.s3tok(packed, frames, want_pre=True)
+    torch.cuda.synchronize()
+    return tok.cpu(), lens, pre.cpu()
+
+
+def _oracle(model, mels):
+    ids, pres = [], []
+    with torch.no_grad():
+        for m in mels:
+            hid, l = model.encode(m, torch.tensor([m.shape[2]]))
+            pres.append(model.fsq_pre(hid)[0])
+            ids.append(torch.tensor(S.tokenize_one(model, m), dtype=torch.int32))
+    return ids, pres
+
+
+@pytest.mark.parametrize("n_layer,prec,tol", [(0, "bf16x3", 2e-4), (1, "bf16x3", 2e-4), (2, "bf16", 0.2), (12, "bf16x3", 5e-4)])
+def test_s3tok_matches_oracle(n_layer, prec, tol):
+    cfg = S.S3Config(n_layer=n_layer)
+    model = S.init_random(S.S3Tokenizer(cfg), seed=1986 + n_layer)
+    eng = Engine(0, prec)
+    eng.load_s3tok(_state(model, cfg), cfg)
+    n = 6 if n_layer < 12 else 3
+    utts = synth.make_set(n, 7 + n_layer, 0.4, 5.0) + [synth.make_set(1, 11, 0.02, 0.03)[0]]
+    mels = _mels(utts)
+    tok, lens, pre = _run(eng, model, mels)
+    ids, pres = _oracle(model, mels)
+    assert lens == [len(i) for i in ids] == [S.token_len(m.shape[2]) for m in mels]  # lengths bit-exact
+    ref_pre = torch.cat(pres)
+    ref_ids = torch.cat(ids)
+    err = float((pre - ref_pre).abs().max())
+    match = float((tok == ref_ids).float().mean())
+    print(f"n_layer={n_layer} prec={prec}: max|pre err|={err:.3e} token match={match:.5f} n={ref_ids.numel()}")
+    assert err <= tol, err
+    if prec == "bf16x3":
+        # every mismatch must sit within 1e-3 of an FSQ rounding boundary (north_star)
+        bad = (tok != ref_ids).nonzero().flatten()
+        for i in bad.tolist():
+            d = (ref_pre[i].abs() - 0.5).abs().min()
+            assert d < 1e-3, (i, float(d))
+        assert match >= 0.999 or ref_ids.numel() < 2000
+    eng.close()
