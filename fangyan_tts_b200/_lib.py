@@ -16,6 +16,13 @@ class FyS3Config(C.Structure):
                [(n, C.c_float) for n in ("rope_theta", "ln_eps", "fsq_scale")]
 
 
+class FyCamConfig(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("feat_dim", "embed_dim", "fcm_channels", "init_channels", "growth", "bn_size",
+                                         "n_blocks")] + \
+               [("layers", C.c_int32 * 4), ("kernel", C.c_int32 * 4), ("dilation", C.c_int32 * 4),
+                ("seg_len", C.c_int32), ("bn_eps", C.c_float)]
+
+
 _P, _I, _Z = C.c_void_p, C.c_int, C.c_size_t
 # name -> (restype, argtypes); mirrors include/fangyan_b200.h one to one
 PROTOTYPES = {
@@ -24,7 +31,7 @@ PROTOTYPES = {
     "fy_last_error": (C.c_char_p, []),
     "fy_set_stream": (_I, [_P, _P]),
     "fy_version": (C.c_char_p, []),
-    "fy_load_campplus": (_I, [_P, C.POINTER(FyTensor), _I]),
+    "fy_load_campplus": (_I, [_P, C.POINTER(FyTensor), _I, C.POINTER(FyCamConfig)]),
     "fy_load_s3tok": (_I, [_P, C.POINTER(FyTensor), _I, C.POINTER(FyS3Config)]),
     "fy_resample": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I]),
     "fy_fbank_workspace_bytes": (_Z, [_I, _I]),

@@ -1,0 +1,171 @@
+// CUDA-core kernels of the CAMPPlus speaker network (row A6): the 1->32 stem convolution, BN+ReLU operand
+// preparation, the context-aware mask (global + 100-frame segment means -> 2-layer MLP -> sigmoid),
+// statistics pooling and the final dense layer.  Convolutions with >= 32 input channels run on the tcgen05 GEMM.
+#pragma once
+#include "fy_common.cuh"
+
+namespace fy {
+namespace camk {
+
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// Stem: Conv2d(1, 32, 3x3, pad 1) + BN + ReLU over (freq, time).  feat is packed [frames, 80] fp32.
+// out: [R100, 82, 32] bf16 channels-last with zero columns at p = 0 and p = 81 (buffer pre-zeroed).
+// rowsrc[r] = feat row of time row r or -1 for guard rows.  w: [32][3 (freq)][3 (time)].
+// grid = R100, block = 320 (80 freq x 4 groups of 8 channels).
+__global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ feat, const int* __restrict__ rowsrc,
+                                                   int R100, const float* __restrict__ w,
+                                                   const float* __restrict__ scale, const float* __restrict__ shift,
+                                                   __nv_bfloat16* __restrict__ out) {
+  const int r = blockIdx.x;
+  const int src = rowsrc[r];
+  if (src < 0) return;
+  __shared__ float in[3][82];
+  __shared__ float sw[32 * 9 + 64];
+  for (int i = threadIdx.x; i < 32 * 9; i += 320) sw[i] = w[i];
+  for (int i = threadIdx.x; i < 64; i += 320) sw[288 + i] = i < 32 ? scale[i] : shift[i - 32];
+  for (int i = threadIdx.x; i < 3 * 82; i += 320) {
+    const int j = i / 82, p = i % 82;
+    const int rr = r + j - 1;
+    const int s = (rr >= 0 && rr < R100) ? rowsrc[rr] : -1;
+    in[j][p] = (s >= 0 && p >= 1 && p <= 80) ? feat[(size_t)s * 80 + p - 1] : 0.f;
+  }
+  __syncthreads();
+  const int f = threadIdx.x % 80, cg = threadIdx.x / 80;
+  float x[3][3];  // [freq i][time j]
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) x[i][j] = in[j][f + i];
+  float y[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cg * 8 + k;
+    float a = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 3; ++j) a += sw[c * 9 + i * 3 + j] * x[i][j];
+    y[k] = fmaxf(a * sw[288 + c] + sw[320 + c], 0.f);
+  }
+  uint4 o;
+  o.x = pack2(y[0], y[1]); o.y = pack2(y[2], y[3]); o.z = pack2(y[4], y[5]); o.w = pack2(y[6], y[7]);
+  *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8) = o;
+}
+
+// mask[g] = time row (g / Q) valid and lo <= g % Q <= hi ? 0 : -1
+__global__ void pos_mask_kernel(const int* __restrict__ rowsrc, int R, int Q, int lo, int hi, int* __restrict__ mask) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= R * Q) return;
+  const int p = g % Q;
+  mask[g] = (rowsrc[g / Q] >= 0 && p >= lo && p <= hi) ? 0 : -1;
+}
+
+// y = bf16(relu(x * scale[c] + shift[c])) for c < C; x fp32 [R, ldx], y bf16 [R, ldy].  4 channels per thread.
+__global__ void __launch_bounds__(256) bnrelu_kernel(const float* __restrict__ x, int ldx, int R, int C,
+                                                     const float* __restrict__ scale, const float* __restrict__ shift,
+                                                     __nv_bfloat16* __restrict__ y, int ldy) {
+  const int per_row = C / 4;
+  const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (size_t)R * per_row) return;
+  const int r = (int)(idx / per_row), c = (int)(idx % per_row) * 4;
+  const float4 v = *reinterpret_cast<const float4*>(x + (size_t)r * ldx + c);
+  const float4 s = __ldg(reinterpret_cast<const float4*>(scale + c));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(shift + c));
+  uint2 o;
+  o.x = pack2(fmaxf(v.x * s.x + b.x, 0.f), fmaxf(v.y * s.y + b.y, 0.f));
+  o.y = pack2(fmaxf(v.z * s.z + b.z, 0.f), fmaxf(v.w * s.w + b.w, 0.f));
+  *reinterpret_cast<uint2*>(y + (size_t)r * ldy + c) = o;
+}
+
+// CAM gate.  h: bf16 [R50, 128] (post BN+ReLU bottleneck).  For utterance u (rows B_u .. B_u + T_u):
+//   ctx[s] = mean over all rows + mean over rows of segment s (seg_len rows, last one partial)
+//   gate[seg_base_u + s][0..32) = sigmoid(W2 relu(W1 ctx + b1) + b2)
+// One block of 128 threads per utterance; supports up to kMaxSeg segments per utterance.
+constexpr int kMaxSegPerUtt = 32;
+__global__ void __launch_bounds__(128) cam_gate_kernel(const __nv_bfloat16* __restrict__ h,
+                                                       const int* __restrict__ utt_B, const int* __restrict__ utt_T,
+                                                       const int* __restrict__ seg_base, int seg_len,
+                                                       const float* __restrict__ w1 /* [64][128] */,
+                                                       const float* __restrict__ b1,
+                                                       const float* __restrict__ w2 /* [32][64] */,
+                                                       const float* __restrict__ b2, float* __restrict__ gate) {
+  __shared__ float seg_sum[kMaxSegPerUtt][128];
+  __shared__ float ctx[128];
+  __shared__ float hid[64];
+  const int u = blockIdx.x, c = threadIdx.x;
+  const int B = utt_B[u], T = utt_T[u];
+  const int nseg = (T + seg_len - 1) / seg_len;
+  float total = 0.f;
+  for (int s = 0; s < nseg; ++s) {
+    const int t1 = min(T, (s + 1) * seg_len);
+    float a = 0.f;
+    for (int t = s * seg_len; t < t1; ++t) a += __bfloat162float(h[(size_t)(B + t) * 128 + c]);
+    seg_sum[s][c] = a;
+    total += a;
+  }
+  const float gmean = total / (float)T;
+  for (int s = 0; s < nseg; ++s) {
+    const int n = min(T, (s + 1) * seg_len) - s * seg_len;
+    __syncthreads();
+    ctx[c] = gmean + seg_sum[s][c] / (float)n;
+    __syncthreads();
+    if (c < 64) {
+      float a = b1[c];
+      for (int k = 0; k < 128; ++k) a += w1[c * 128 + k] * ctx[k];
+      hid[c] = fmaxf(a, 0.f);
+    }
+    __syncthreads();
+    if (c < 32) {
+      float a = b2[c];
+      for (int k = 0; k < 64; ++k) a += w2[c * 64 + k] * hid[k];
+      gate[(size_t)(seg_base[u] + s) * 32 + c] = 1.0f / (1.0f + expf(-a));
+    }
+  }
+}
+
+// Statistics pooling after BN+ReLU: stats[u] = [mean(1..C), std_unbiased(1..C)] over the utterance's rows.
+// x fp32 [R50, ldx]; one block per utterance, one thread per channel (C <= 512).
+__global__ void __launch_bounds__(512) stats_kernel(const float* __restrict__ x, int ldx, int C,
+                                                    const int* __restrict__ utt_B, const int* __restrict__ utt_T,
+                                                    const float* __restrict__ scale, const float* __restrict__ shift,
+                                                    float* __restrict__ stats) {
+  const int u = blockIdx.x, c = threadIdx.x;
+  if (c >= C) return;
+  const int B = utt_B[u], T = utt_T[u];
+  const float s = scale[c], b = shift[c];
+  float sum = 0.f;
+  for (int t = 0; t < T; ++t) sum += fmaxf(x[(size_t)(B + t) * ldx + c] * s + b, 0.f);
+  const float mean = sum / (float)T;
+  float ss = 0.f;
+  for (int t = 0; t < T; ++t) {
+    const float d = fmaxf(x[(size_t)(B + t) * ldx + c] * s + b, 0.f) - mean;
+    ss += d * d;
+  }
+  stats[(size_t)u * 2 * C + c] = mean;
+  stats[(size_t)u * 2 * C + C + c] = sqrtf(ss / (float)(T - 1));
+}
+
+// emb[u][o] = (sum_k W[o][k] stats[u][k]) * scale[o] + shift[o]; one block per utterance, one warp per 8 outputs.
+__global__ void __launch_bounds__(256) dense_kernel(const float* __restrict__ stats, int K, int O,
+                                                    const float* __restrict__ w, const float* __restrict__ scale,
+                                                    const float* __restrict__ shift, float* __restrict__ emb) {
+  extern __shared__ float sx[];
+  const int u = blockIdx.x;
+  for (int i = threadIdx.x; i < K; i += blockDim.x) sx[i] = stats[(size_t)u * K + i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int o = warp; o < O; o += 8) {
+    float a = 0.f;
+    for (int k = lane; k < K; k += 32) a += w[(size_t)o * K + k] * sx[k];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
+    if (lane == 0) emb[(size_t)u * O + o] = a * scale[o] + shift[o];
+  }
+}
+
+}  // namespace camk
+}  // namespace fy

@@ -1,8 +1,480 @@
+// CAMPPlus speaker network (row A6): weight preparation (BatchNorm folding, conv weights -> GEMM operands),
+// per-call planning and the launch sequence.  Replaces ort_session.run() on campplus.onnx
+// (tools/extract_embedding.py:36-41).
+//
+// Layout: utterances are PACKED along time with zero guard rows instead of padding.  At 50 Hz utterance u owns
+// rows [B_u, B_u + T2_u) with two guard rows after it (dilation-2 convolutions); at 100 Hz it owns rows
+// [2*B_u + 2, 2*B_u + 2 + T_u), so the stride-2 TDNN is a GEMM over a "two time rows per row" view.  The 2-D FCM
+// head keeps activations channels-last as [time row][freq position + 2 pads][32]; every 3x3 convolution is one
+// tcgen05 GEMM with one K-block per tap (row offset = dt * positions_per_row + df).
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "fy_cam_kernels.cuh"
 #include "fy_common.cuh"
-namespace fy { void cam_free_plan(Ctx*) {} }
+
+namespace fy {
+namespace {
+
+struct BN { float* scale = nullptr; float* shift = nullptr; };
+
+struct ConvW {           // a 32->32 FCM convolution as a GEMM B operand [32, taps * 64]
+  __nv_bfloat16* w = nullptr;
+  CUtensorMap map;
+  BN bn;
+};
+struct ResW { ConvW c1, c2, sc; bool stride2 = false; };
+
+struct DenseW {
+  int cin = 0;
+  BN bn1, bn2;
+  __nv_bfloat16 *w1 = nullptr, *wl = nullptr;
+  CUtensorMap m1, ml;
+  float *cw1 = nullptr, *cb1 = nullptr, *cw2 = nullptr, *cb2 = nullptr;
+};
+struct TransW { int cin = 0, cout = 0; BN bn; __nv_bfloat16* w = nullptr; CUtensorMap m; };
+
+struct CamPlan {
+  fy_campplus_config cfg;
+  float* stem_w = nullptr; BN stem_bn;
+  std::vector<ResW> res;
+  ConvW fcm_out;
+  __nv_bfloat16* tdnn_w = nullptr; CUtensorMap tdnn_m; BN tdnn_bn;
+  std::vector<std::vector<DenseW>> blocks;
+  std::vector<TransW> trans;
+  BN out_bn;
+  float* dense_w = nullptr; BN dense_bn;
+  std::vector<void*> owned;
+  int* h_meta = nullptr; size_t h_meta_cap = 0; cudaEvent_t meta_ev = nullptr;
+};
+
+struct Loader {
+  CamPlan* p; const fy_tensor* t; int n;
+  const fy_tensor* get(const std::string& name) const {
+    for (int i = 0; i < n; ++i) if (name == t[i].name) return &t[i];
+    return nullptr;
+  }
+};
+int64_t numel(const fy_tensor* t) { int64_t n = 1; for (int i = 0; i < t->ndim; ++i) n *= t->shape[i]; return n; }
+
+template <typename T>
+int dev_upload(CamPlan* p, const std::vector<T>& h, T** d) {
+  FY_CUDA(cudaMalloc(d, h.size() * sizeof(T)));
+  p->owned.push_back(*d);
+  FY_CUDA(cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return FY_OK;
+}
+int upload_bf16(CamPlan* p, const std::vector<float>& h, __nv_bfloat16** d) {
+  std::vector<__nv_bfloat16> b(h.size());
+  for (size_t i = 0; i < h.size(); ++i) b[i] = __float2bfloat16_rn(h[i]);
+  return dev_upload(p, b, d);
+}
+
+#define GET(var, name, count)                                                                              \
+  const fy_tensor* var = L.get(name);                                                                      \
+  FY_CHECK(var != nullptr, FY_ERR_ARG, "fy_load_campplus: missing tensor '%s'", std::string(name).c_str()); \
+  FY_CHECK(numel(var) == (int64_t)(count), FY_ERR_ARG, "fy_load_campplus: '%s' has %lld elements, expected %lld", \
+           std::string(name).c_str(), (long long)numel(var), (long long)(count))
+
+// BatchNorm (eval) -> y = x * scale + shift
+int load_bn(const Loader& L, const std::string& pre, int C, bool affine, BN* bn) {
+  GET(mean, pre + ".running_mean", C);
+  GET(var, pre + ".running_var", C);
+  std::vector<float> sc(C), sh(C);
+  const fy_tensor *w = nullptr, *b = nullptr;
+  if (affine) {
+    w = L.get(pre + ".weight");
+    b = L.get(pre + ".bias");
+    FY_CHECK(w && b && numel(w) == C && numel(b) == C, FY_ERR_ARG, "fy_load_campplus: missing affine terms of '%s'", pre.c_str());
+  }
+  for (int c = 0; c < C; ++c) {
+    const float inv = 1.0f / sqrtf(var->h_data[c] + L.p->cfg.bn_eps);
+    sc[c] = (affine ? w->h_data[c] : 1.0f) * inv;
+    sh[c] = (affine ? b->h_data[c] : 0.0f) - mean->h_data[c] * sc[c];
+  }
+  FY_TRY(dev_upload(L.p, sc, &bn->scale));
+  FY_TRY(dev_upload(L.p, sh, &bn->shift));
+  return FY_OK;
+}
+
+// Conv2d weight [32, 32, kf, kt] (kf = freq taps, kt = time taps) -> B [32, kf*kt*64]: tap (dt, df) occupies
+// columns [(dt_i*kf + df_i)*64, +32); the upper 32 columns of each K-block are zero.
+int load_fcm_conv(const Loader& L, const std::string& name, int kf, int kt, const std::string& bn_name, ConvW* out) {
+  GET(w, name, 32 * 32 * kf * kt);
+  std::vector<float> b((size_t)32 * kf * kt * 64, 0.f);
+  for (int o = 0; o < 32; ++o)
+    for (int c = 0; c < 32; ++c)
+      for (int i = 0; i < kf; ++i)
+        for (int j = 0; j < kt; ++j)
+          b[(size_t)o * kf * kt * 64 + (j * kf + i) * 64 + c] = w->h_data[((o * 32 + c) * kf + i) * kt + j];
+  FY_TRY(upload_bf16(L.p, b, &out->w));
+  FY_TRY(make_tmap_bf16(&out->map, out->w, 32, (uint64_t)kf * kt * 64, (uint64_t)kf * kt * 64, 32));
+  return load_bn(L, bn_name, 32, true, &out->bn);
+}
+
+size_t align_up(size_t x, size_t a = 1024) { return (x + a - 1) / a * a; }
+
+struct Layout {
+  int n_utts, R50, R100, n_seg;
+  size_t m_B, m_T2, m_segbase, m_rowsrc, m_rowseg, meta_ints;
+  size_t o_meta, o_m42s, o_m42, o_m22s, o_m22, o_m11s, o_x0, o_y40, o_s40, o_z40a, o_z40b, o_y20, o_s20, o_z20a, o_z20b,
+      o_fcm, o_cat[4], o_hin, o_hb, o_gate, o_stats, total;
+};
+
+Layout make_layout(const CamPlan* p, int n_utts, int r50, int n_seg) {
+  Layout l;
+  l.n_utts = n_utts; l.R50 = r50; l.R100 = 2 * r50 + 4; l.n_seg = n_seg;
+  l.m_B = 0; l.m_T2 = n_utts; l.m_segbase = 2 * (size_t)n_utts; l.m_rowsrc = 3 * (size_t)n_utts;
+  l.m_rowseg = l.m_rowsrc + l.R100; l.meta_ints = l.m_rowseg + r50;
+  const size_t R = l.R100;
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes); return at; };
+  l.o_meta = take(l.meta_ints * 4);
+  l.o_m42s = take(R * 41 * 4); l.o_m42 = take(R * 42 * 4);
+  l.o_m22s = take(R * 21 * 4); l.o_m22 = take(R * 22 * 4); l.o_m11s = take(R * 11 * 4);
+  l.o_x0 = take(R * 82 * 64);
+  l.o_y40 = take(R * 42 * 64); l.o_s40 = take(R * 42 * 64); l.o_z40a = take(R * 42 * 64); l.o_z40b = take(R * 42 * 64);
+  l.o_y20 = take(R * 22 * 64); l.o_s20 = take(R * 22 * 64); l.o_z20a = take(R * 22 * 64); l.o_z20b = take(R * 22 * 64);
+  l.o_fcm = take(R * 320 * 2);
+  int c = p->cfg.init_channels;
+  for (int b = 0; b < p->cfg.n_blocks; ++b) {
+    const int ctot = c + p->cfg.layers[b] * p->cfg.growth;
+    l.o_cat[b] = take((size_t)r50 * ctot * 4);
+    c = ctot / 2;
+  }
+  l.o_cat[p->cfg.n_blocks] = take((size_t)r50 * c * 4);
+  l.o_hin = take((size_t)r50 * 1024 * 2);
+  l.o_hb = take((size_t)r50 * 128 * 2);
+  l.o_gate = take((size_t)n_seg * 32 * 4);
+  l.o_stats = take((size_t)n_utts * 2 * c * 4);
+  l.total = o;
+  return l;
+}
+
+}  // namespace
+
+void cam_free_plan(Ctx* c) {
+  CamPlan* p = reinterpret_cast<CamPlan*>(c->cam_plan);
+  if (!p) return;
+  for (void* d : p->owned) cudaFree(d);
+  if (p->h_meta) cudaFreeHost(p->h_meta);
+  if (p->meta_ev) cudaEventDestroy(p->meta_ev);
+  delete p;
+  c->cam_plan = nullptr;
+}
+
+}  // namespace fy
+
 using namespace fy;
+
 extern "C" {
-int fy_load_campplus(fy_ctx*, const fy_tensor*, int) { set_error("not implemented"); return FY_ERR_STATE; }
-size_t fy_campplus_workspace_bytes(fy_ctx*, int, int) { return 0; }
-int fy_campplus_forward(fy_ctx*, const float*, const int32_t*, const int32_t*, int, float*, void*, size_t) { set_error("not implemented"); return FY_ERR_STATE; }
+
+int fy_load_campplus(fy_ctx* ctx, const fy_tensor* t, int n, const fy_campplus_config* cfg) {
+  FY_CHECK(ctx && t && cfg && n > 0, FY_ERR_ARG, "fy_load_campplus: NULL argument");
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  FY_CUDA(cudaSetDevice(c->device));
+  FY_CHECK(cfg->feat_dim == 80 && cfg->fcm_channels == 32 && cfg->init_channels == 128 && cfg->growth == 32 &&
+               cfg->bn_size == 4 && cfg->n_blocks == 3,
+           FY_ERR_ARG, "fy_load_campplus: kernels are built for feat 80, FCM 32 ch, init 128, growth 32, bn_size 4, 3 blocks");
+  for (int b = 0; b < cfg->n_blocks; ++b)
+    FY_CHECK(cfg->kernel[b] == 3 && cfg->dilation[b] >= 1 && cfg->dilation[b] <= 2, FY_ERR_ARG,
+             "fy_load_campplus: block %d needs kernel 3 and dilation 1 or 2", b);
+  cam_free_plan(c);
+  CamPlan* p = new CamPlan();
+  c->cam_plan = p;
+  p->cfg = *cfg;
+  Loader L{p, t, n};
+  {
+    GET(w, "head.conv1.weight", 32 * 9);
+    std::vector<float> h(w->h_data, w->h_data + 288);
+    FY_TRY(dev_upload(p, h, &p->stem_w));
+    FY_TRY(load_bn(L, "head.bn1", 32, true, &p->stem_bn));
+  }
+  p->res.resize(4);
+  for (int i = 0; i < 4; ++i) {
+    const std::string pre = "head.blocks." + std::to_string(i);
+    ResW& r = p->res[i];
+    r.stride2 = (i % 2) == 0;
+    FY_TRY(load_fcm_conv(L, pre + ".conv1.weight", 3, 3, pre + ".bn1", &r.c1));
+    FY_TRY(load_fcm_conv(L, pre + ".conv2.weight", 3, 3, pre + ".bn2", &r.c2));
+    if (r.stride2) FY_TRY(load_fcm_conv(L, pre + ".sc_conv.weight", 1, 1, pre + ".sc_bn", &r.sc));
+  }
+  FY_TRY(load_fcm_conv(L, "head.conv2.weight", 3, 3, "head.bn2", &p->fcm_out));
+  {
+    GET(w, "tdnn.weight", 128 * 320 * 5);
+    std::vector<float> b((size_t)128 * 1600);
+    for (int o = 0; o < 128; ++o)
+      for (int ch = 0; ch < 32; ++ch)
+        for (int f = 0; f < 10; ++f)
+          for (int k = 0; k < 5; ++k)
+            b[(size_t)o * 1600 + k * 320 + f * 32 + ch] = w->h_data[((size_t)o * 320 + ch * 10 + f) * 5 + k];
+    FY_TRY(upload_bf16(p, b, &p->tdnn_w));
+    FY_TRY(make_tmap_bf16(&p->tdnn_m, p->tdnn_w, 128, 1600, 1600, 128));
+    FY_TRY(load_bn(L, "tdnn_nl.0", 128, true, &p->tdnn_bn));
+  }
+  int ch = cfg->init_channels;
+  p->blocks.resize(cfg->n_blocks);
+  p->trans.resize(cfg->n_blocks);
+  for (int b = 0; b < cfg->n_blocks; ++b) {
+    p->blocks[b].resize(cfg->layers[b]);
+    for (int l = 0; l < cfg->layers[b]; ++l) {
+      DenseW& d = p->blocks[b][l];
+      d.cin = ch + l * cfg->growth;
+      const std::string pre = "blocks." + std::to_string(b) + "." + std::to_string(l);
+      FY_TRY(load_bn(L, pre + ".nl1.0", d.cin, true, &d.bn1));
+      FY_TRY(load_bn(L, pre + ".nl2.0", 128, true, &d.bn2));
+      GET(w1, pre + ".lin1.weight", 128 * d.cin);
+      FY_TRY(upload_bf16(p, std::vector<float>(w1->h_data, w1->h_data + 128 * d.cin), &d.w1));
+      FY_TRY(make_tmap_bf16(&d.m1, d.w1, 128, d.cin, d.cin, 128));
+      GET(wl, pre + ".cam.local.weight", 32 * 128 * 3);
+      std::vector<float> bl((size_t)32 * 384);
+      for (int o = 0; o < 32; ++o)
+        for (int cc = 0; cc < 128; ++cc)
+          for (int k = 0; k < 3; ++k) bl[(size_t)o * 384 + k * 128 + cc] = wl->h_data[(o * 128 + cc) * 3 + k];
+      FY_TRY(upload_bf16(p, bl, &d.wl));
+      FY_TRY(make_tmap_bf16(&d.ml, d.wl, 32, 384, 384, 32));
+      GET(a1, pre + ".cam.lin1.weight", 64 * 128); GET(a1b, pre + ".cam.lin1.bias", 64);
+      GET(a2, pre + ".cam.lin2.weight", 32 * 64); GET(a2b, pre + ".cam.lin2.bias", 32);
+      FY_TRY(dev_upload(p, std::vector<float>(a1->h_data, a1->h_data + 64 * 128), &d.cw1));
+      FY_TRY(dev_upload(p, std::vector<float>(a1b->h_data, a1b->h_data + 64), &d.cb1));
+      FY_TRY(dev_upload(p, std::vector<float>(a2->h_data, a2->h_data + 32 * 64), &d.cw2));
+      FY_TRY(dev_upload(p, std::vector<float>(a2b->h_data, a2b->h_data + 32), &d.cb2));
+    }
+    ch += cfg->layers[b] * cfg->growth;
+    TransW& tr = p->trans[b];
+    tr.cin = ch; tr.cout = ch / 2;
+    FY_CHECK(tr.cin <= 1024 && tr.cout % 128 == 0, FY_ERR_ARG, "fy_load_campplus: block %d width %d unsupported", b, ch);
+    const std::string pre = "transits." + std::to_string(b);
+    FY_TRY(load_bn(L, pre + ".nl.0", tr.cin, true, &tr.bn));
+    GET(w, pre + ".lin.weight", (int64_t)tr.cout * tr.cin);
+    FY_TRY(upload_bf16(p, std::vector<float>(w->h_data, w->h_data + (size_t)tr.cout * tr.cin), &tr.w));
+    FY_TRY(make_tmap_bf16(&tr.m, tr.w, tr.cout, tr.cin, tr.cin, gemm_block_n(tr.cout)));
+    ch = tr.cout;
+  }
+  FY_CHECK(ch <= 512, FY_ERR_ARG, "fy_load_campplus: final width %d > 512", ch);
+  FY_TRY(load_bn(L, "out_nl.0", ch, true, &p->out_bn));
+  {
+    GET(w, "dense.weight", (int64_t)cfg->embed_dim * 2 * ch);
+    FY_TRY(dev_upload(p, std::vector<float>(w->h_data, w->h_data + (size_t)cfg->embed_dim * 2 * ch), &p->dense_w));
+    FY_TRY(load_bn(L, "dense_bn", cfg->embed_dim, false, &p->dense_bn));
+  }
+  FY_CUDA(cudaEventCreateWithFlags(&p->meta_ev, cudaEventDisableTiming));
+  return FY_OK;
+}
+
+size_t fy_campplus_workspace_bytes(fy_ctx* ctx, int n_utts, int total_frames) {
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  if (!c || !c->cam_plan || n_utts <= 0) return 0;
+  CamPlan* p = reinterpret_cast<CamPlan*>(c->cam_plan);
+  const int r50 = total_frames / 2 + 3 * n_utts + 2;
+  const int nseg = r50 / p->cfg.seg_len + n_utts + 1;
+  return make_layout(p, n_utts, r50, nseg).total;
+}
+
+}  // extern "C"
+
+namespace {
+
+// one FCM 3x3 / 1x1 convolution launch
+struct FcmConv {
+  const ConvW* w; const __nv_bfloat16* in; int in_fp;  // input buffer [R100, in_fp, 32]
+  bool stride2; bool k3;                                // stride 2 in frequency; 3x3 (else 1x1)
+  __nv_bfloat16* out; int out_fp; int out_add;          // output [R100, out_fp, 32], first valid slot
+  const int* mask; const __nv_bfloat16* resid; bool relu;
+};
+
+int run_fcm_conv(Ctx* c, const FcmConv& f, int R100) {
+  GemmArgs g;
+  g.N = 32;
+  g.tmap_b = f.w->map;
+  const int Q = f.stride2 ? f.in_fp / 2 : f.in_fp;  // GEMM rows per time row
+  g.M = R100 * Q;
+  if (f.stride2) {
+    FY_TRY(make_tmap_bf16(&g.tmap_a, f.in, (uint64_t)R100 * Q, 64, 64, 128));
+  } else {
+    FY_TRY(make_tmap_bf16(&g.tmap_a, f.in, (uint64_t)R100 * Q, 32, 32, 128));
+  }
+  if (f.k3) {
+    for (int j = 0; j < 3; ++j)      // time tap dt = j - 1
+      for (int i = 0; i < 3; ++i) {  // freq tap df = i - 1
+        GemmSeg sg;
+        sg.b_col = (j * 3 + i) * 64;
+        sg.nkb = 1;
+        if (f.stride2) { sg.a_row_off = (j - 1) * Q + (i == 2 ? 1 : 0); sg.a_col = (i == 1) ? 32 : 0; }
+        else { sg.a_row_off = (j - 1) * Q + (i - 1); sg.a_col = 0; }
+        g.seg[g.nseg++] = sg;
+      }
+  } else {
+    g.seg[g.nseg++] = GemmSeg{0, f.stride2 ? 32 : 0, 0, 1};
+  }
+  g.epi.mode = EPI_BF16;
+  g.epi.act = f.relu ? ACT_RELU : ACT_NONE;
+  g.epi.out = f.out; g.epi.ldo = 32;
+  g.epi.scale = f.w->bn.scale; g.epi.bias = f.w->bn.shift;
+  g.epi.row_idx = f.mask;
+  g.epi.resid = f.resid;
+  if (f.stride2 || f.out_fp != Q) { g.epi.remap_q = Q; g.epi.remap_fp = f.out_fp; g.epi.remap_add = f.out_add; }
+  return launch_gemm(g, c->num_sms, c->stream);
+}
+
+}  // namespace
+
+extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t* frame_off, const int32_t* h_frame_off,
+                                   int n_utts, float* emb, void* ws, size_t ws_bytes) {
+  FY_CHECK(ctx && feat && frame_off && h_frame_off && emb && ws, FY_ERR_ARG, "fy_campplus_forward: NULL argument");
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  CamPlan* p = reinterpret_cast<CamPlan*>(c->cam_plan);
+  FY_CHECK(p != nullptr, FY_ERR_STATE, "fy_campplus_forward: call fy_load_campplus first");
+  FY_CHECK(n_utts > 0, FY_ERR_ARG, "fy_campplus_forward: n_utts must be positive");
+  FY_CHECK((reinterpret_cast<uintptr_t>(ws) & 255) == 0, FY_ERR_ARG, "fy_campplus_forward: workspace must be 256-byte aligned");
+  const fy_campplus_config& cf = p->cfg;
+  cudaStream_t st = c->stream;
+  (void)frame_off;
+
+  // ---- plan
+  std::vector<int> B(n_utts), T2(n_utts), SB(n_utts);
+  int row = 0, nseg = 0;
+  for (int u = 0; u < n_utts; ++u) {
+    const int T = h_frame_off[u + 1] - h_frame_off[u];
+    FY_CHECK(T >= 3, FY_ERR_ARG, "fy_campplus_forward: utterance %d has %d frames (need >= 3)", u, T);
+    T2[u] = (T - 1) / 2 + 1;
+    const int ns = (T2[u] + cf.seg_len - 1) / cf.seg_len;
+    FY_CHECK(ns <= camk::kMaxSegPerUtt, FY_ERR_ARG, "fy_campplus_forward: utterance %d too long (%d frames)", u, T);
+    B[u] = row; SB[u] = nseg;
+    row += T2[u] + 2;
+    nseg += ns;
+  }
+  Layout lay = make_layout(p, n_utts, row, nseg);
+  FY_CHECK(lay.total <= ws_bytes, FY_ERR_NOMEM, "fy_campplus_forward: workspace %zu < %zu bytes", ws_bytes, lay.total);
+  const int R50 = lay.R50, R100 = lay.R100;
+  if (p->h_meta_cap < lay.meta_ints) {
+    if (p->h_meta) { FY_CUDA(cudaEventSynchronize(p->meta_ev)); FY_CUDA(cudaFreeHost(p->h_meta)); }
+    p->h_meta_cap = lay.meta_ints * 2;
+    FY_CUDA(cudaMallocHost(&p->h_meta, p->h_meta_cap * 4));
+  } else {
+    FY_CUDA(cudaEventSynchronize(p->meta_ev));
+  }
+  int* hm = p->h_meta;
+  std::fill(hm, hm + lay.meta_ints, -1);
+  for (int u = 0; u < n_utts; ++u) {
+    hm[lay.m_B + u] = B[u]; hm[lay.m_T2 + u] = T2[u]; hm[lay.m_segbase + u] = SB[u];
+    const int T = h_frame_off[u + 1] - h_frame_off[u];
+    for (int t = 0; t < T; ++t) hm[lay.m_rowsrc + 2 * B[u] + 2 + t] = h_frame_off[u] + t;
+    for (int t = 0; t < T2[u]; ++t) hm[lay.m_rowseg + B[u] + t] = SB[u] + t / cf.seg_len;
+  }
+  uint8_t* base = reinterpret_cast<uint8_t*>(ws);
+  int* d_meta = reinterpret_cast<int*>(base + lay.o_meta);
+  FY_CUDA(cudaMemcpyAsync(d_meta, hm, lay.meta_ints * 4, cudaMemcpyHostToDevice, st));
+  FY_CUDA(cudaEventRecord(p->meta_ev, st));
+  const int *d_B = d_meta + lay.m_B, *d_T2 = d_meta + lay.m_T2, *d_segbase = d_meta + lay.m_segbase;
+  const int *d_rowsrc = d_meta + lay.m_rowsrc, *d_rowseg = d_meta + lay.m_rowseg;
+  auto I = [&](size_t off) { return reinterpret_cast<int*>(base + off); };
+  auto H = [&](size_t off) { return reinterpret_cast<__nv_bfloat16*>(base + off); };
+  auto Fp = [&](size_t off) { return reinterpret_cast<float*>(base + off); };
+  int *m42s = I(lay.o_m42s), *m42 = I(lay.o_m42), *m22s = I(lay.o_m22s), *m22 = I(lay.o_m22), *m11s = I(lay.o_m11s);
+  // zero the FCM activation buffers (pads and guard rows must read as zero) -- one contiguous span
+  FY_CUDA(cudaMemsetAsync(base + lay.o_x0, 0, lay.o_fcm - lay.o_x0, st));
+  {
+    auto mk = [&](int Q, int lo, int hi, int* m) {
+      const int n = R100 * Q;
+      camk::pos_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_rowsrc, R100, Q, lo, hi, m);
+    };
+    mk(41, 0, 39, m42s); mk(42, 1, 40, m42); mk(21, 0, 19, m22s); mk(22, 1, 20, m22); mk(11, 0, 9, m11s);
+    camk::stem_kernel<<<R100, 320, 0, st>>>(feat, d_rowsrc, R100, p->stem_w, p->stem_bn.scale, p->stem_bn.shift, H(lay.o_x0));
+    FY_CUDA(cudaGetLastError());
+  }
+  // ---- FCM residual stages
+  {
+    struct Stage { const __nv_bfloat16* in; int in_fp; __nv_bfloat16 *y, *s, *za, *zb; int fp; const int *ms, *m; };
+    Stage stg[2] = {{H(lay.o_x0), 82, H(lay.o_y40), H(lay.o_s40), H(lay.o_z40a), H(lay.o_z40b), 42, m42s, m42},
+                    {H(lay.o_z40b), 42, H(lay.o_y20), H(lay.o_s20), H(lay.o_z20a), H(lay.o_z20b), 22, m22s, m22}};
+    for (int s = 0; s < 2; ++s) {
+      const Stage& S = stg[s];
+      const ResW& r0 = p->res[2 * s];
+      const ResW& r1 = p->res[2 * s + 1];
+      FY_TRY(run_fcm_conv(c, FcmConv{&r0.c1, S.in, S.in_fp, true, true, S.y, S.fp, 1, S.ms, nullptr, true}, R100));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r0.sc, S.in, S.in_fp, true, false, S.s, S.fp, 1, S.ms, nullptr, false}, R100));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r0.c2, S.y, S.fp, false, true, S.za, S.fp, 0, S.m, S.s, true}, R100));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r1.c1, S.za, S.fp, false, true, S.y, S.fp, 0, S.m, nullptr, true}, R100));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r1.c2, S.y, S.fp, false, true, S.zb, S.fp, 0, S.m, S.za, true}, R100));
+    }
+    FY_TRY(run_fcm_conv(c, FcmConv{&p->fcm_out, H(lay.o_z20b), 22, true, true, H(lay.o_fcm), 10, 0, m11s, nullptr, true}, R100));
+  }
+  // ---- TDNN: Conv1d(320 -> 128, k5, stride 2, pad 2) + BN + ReLU -> concat block 0, columns [0, 128)
+  int ctot[4];
+  {
+    int ch = cf.init_channels;
+    for (int b = 0; b < cf.n_blocks; ++b) { ctot[b] = ch + cf.layers[b] * cf.growth; ch = ctot[b] / 2; }
+    ctot[cf.n_blocks] = ch;
+  }
+  {
+    GemmArgs g;
+    FY_TRY(make_tmap_bf16(&g.tmap_a, H(lay.o_fcm), R100 / 2, 640, 640, 128));
+    g.tmap_b = p->tdnn_m;
+    g.M = R50; g.N = 128;
+    g.seg[g.nseg++] = GemmSeg{0, 0, 0, 10};
+    g.seg[g.nseg++] = GemmSeg{1, 0, 640, 10};
+    g.seg[g.nseg++] = GemmSeg{2, 0, 1280, 5};
+    g.epi.mode = EPI_F32_STORE; g.epi.act = ACT_RELU; g.epi.out = Fp(lay.o_cat[0]); g.epi.ldo = ctot[0];
+    g.epi.scale = p->tdnn_bn.scale; g.epi.bias = p->tdnn_bn.shift; g.epi.row_idx = d_rowseg;
+    FY_TRY(launch_gemm(g, c->num_sms, st));
+  }
+  // ---- dense blocks
+  __nv_bfloat16* hin = H(lay.o_hin);
+  __nv_bfloat16* hb = H(lay.o_hb);
+  float* gate = Fp(lay.o_gate);
+  CUtensorMap m_hb;
+  FY_TRY(make_tmap_bf16(&m_hb, hb, R50, 128, 128, 128));
+  for (int b = 0; b < cf.n_blocks; ++b) {
+    float* cat = Fp(lay.o_cat[b]);
+    const int ld = ctot[b];
+    const int dil = cf.dilation[b];
+    for (int l = 0; l < cf.layers[b]; ++l) {
+      const DenseW& d = p->blocks[b][l];
+      {
+        const size_t n = (size_t)R50 * (d.cin / 4);
+        camk::bnrelu_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(cat, ld, R50, d.cin, d.bn1.scale, d.bn1.shift, hin, 1024);
+      }
+      {
+        GemmArgs g;
+        FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, d.cin, 1024, 128));
+        g.tmap_b = d.m1; g.M = R50; g.N = 128;
+        g.seg[g.nseg++] = GemmSeg{0, 0, 0, (d.cin + 63) / 64};
+        g.epi.mode = EPI_BF16; g.epi.act = ACT_RELU; g.epi.out = hb; g.epi.ldo = 128;
+        g.epi.scale = d.bn2.scale; g.epi.bias = d.bn2.shift; g.epi.row_idx = d_rowseg;
+        FY_TRY(launch_gemm(g, c->num_sms, st));
+      }
+      camk::cam_gate_kernel<<<n_utts, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
+      {
+        GemmArgs g;
+        g.tmap_a = m_hb; g.tmap_b = d.ml; g.M = R50; g.N = 32;
+        for (int k = 0; k < 3; ++k) g.seg[g.nseg++] = GemmSeg{(k - 1) * dil, 0, k * 128, 2};
+        g.epi.mode = EPI_F32_STORE; g.epi.out = cat; g.epi.ldo = ld; g.epi.col_off = d.cin;
+        g.epi.row_idx = d_rowseg; g.epi.row_gate = gate;
+        FY_TRY(launch_gemm(g, c->num_sms, st));
+      }
+    }
+    const TransW& tr = p->trans[b];
+    {
+      const size_t n = (size_t)R50 * (tr.cin / 4);
+      camk::bnrelu_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(cat, ld, R50, tr.cin, tr.bn.scale, tr.bn.shift, hin, 1024);
+      GemmArgs g;
+      FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, tr.cin, 1024, 128));
+      g.tmap_b = tr.m; g.M = R50; g.N = tr.cout;
+      g.seg[g.nseg++] = GemmSeg{0, 0, 0, (tr.cin + 63) / 64};
+      g.epi.mode = EPI_F32_STORE; g.epi.out = Fp(lay.o_cat[b + 1]); g.epi.ldo = ctot[b + 1];
+      g.epi.row_idx = d_rowseg;
+      FY_TRY(launch_gemm(g, c->num_sms, st));
+    }
+  }
+  // ---- BN + ReLU -> statistics pooling -> dense -> BN
+  const int C = ctot[cf.n_blocks];
+  float* stats = Fp(lay.o_stats);
+  camk::stats_kernel<<<n_utts, 512, 0, st>>>(Fp(lay.o_cat[cf.n_blocks]), C, C, d_B, d_T2, p->out_bn.scale, p->out_bn.shift, stats);
+  camk::dense_kernel<<<n_utts, 256, 2 * C * 4, st>>>(stats, 2 * C, cf.embed_dim, p->dense_w, p->dense_bn.scale,
+                                                     p->dense_bn.shift, emb);
+  FY_CUDA(cudaGetLastError());
+  return FY_OK;
 }

@@ -59,6 +59,9 @@ struct GemmEpi {
   const float* bias = nullptr;     // [N] per-column addend or null
   const int* row_idx = nullptr;    // [M] or null: rows with row_idx < 0 are written as zero
   const float* row_gate = nullptr; // [*, N] or null: multiply by row_gate[row_idx[row] * N + n] (CAM mask)
+  const __nv_bfloat16* resid = nullptr;  // EPI_BF16 only: bf16 tensor (same rows / ldo / col_off as out) added before act
+  // output row remap: out_row = (row / remap_q) * remap_fp + row % remap_q + remap_add   (remap_q == 0: identity)
+  int remap_q = 0, remap_fp = 0, remap_add = 0;
 };
 
 struct GemmArgs {

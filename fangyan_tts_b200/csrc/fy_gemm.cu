@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       int ridx = 0;
       if (e.row_idx) ridx = row_ok ? __ldg(e.row_idx + row) : -1;
       const bool keep = ridx >= 0;
+      const size_t orow = e.remap_q ? (size_t)(row / e.remap_q) * e.remap_fp + row % e.remap_q + e.remap_add : (size_t)row;
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
@@ -171,9 +172,25 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         ptx::tmem_ld_wait();
         if (row_ok) {
           float x[32];
+          const size_t col = (size_t)e.col_off + n0 + c * 32;
+          float rs[32];
+          if (e.resid) {
+            const uint4* rp = reinterpret_cast<const uint4*>(e.resid + orow * e.ldo + col);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 w = __ldg(rp + j);
+              const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                rs[8 * j + 2 * k] = __uint_as_float(ww[k] << 16);
+                rs[8 * j + 2 * k + 1] = __uint_as_float(ww[k] & 0xffff0000u);
+              }
+            }
+          }
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             float t = __uint_as_float(v[j]) * s_scale[c * 32 + j] + s_bias[c * 32 + j];
+            if (e.resid) t += rs[j];
             if (e.act == ACT_GELU) t = gelu_erf(t);
             else if (e.act == ACT_RELU) t = fmaxf(t, 0.0f);
             x[j] = t;
@@ -190,9 +207,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 #pragma unroll
             for (int j = 0; j < 32; ++j) x[j] = 0.0f;
           }
-          const size_t col = (size_t)e.col_off + n0 + c * 32;
           if (e.mode == EPI_BF16) {
-            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + (size_t)row * e.ldo;
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + orow * e.ldo;
             uint4* dst = reinterpret_cast<uint4*>(o + col);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -218,7 +234,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
               }
             }
           } else {
-            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + (size_t)row * e.ldo + col);
+            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow * e.ldo + col);
             if (e.mode == EPI_F32_ADD) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) {

@@ -9,7 +9,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import FyS3Config, FyTensor, check
+from ._lib import FyCamConfig, FyS3Config, FyTensor, check
 
 PREC = {"bf16": 0, "bf16x3": 1}
 EMBED_DIM = 192
@@ -110,9 +110,15 @@ class Engine:
                 arr[i].shape[j] = s
         return arr, keep
 
-    def load_campplus(self, state: dict):
+    def load_campplus(self, state: dict, cfg):
         arr, keep = self._tensor_table(state)
-        check(self.lib.fy_load_campplus(self.h, arr, len(state)))
+        c = FyCamConfig()
+        c.feat_dim, c.embed_dim, c.fcm_channels = cfg.feat_dim, cfg.embed_dim, cfg.fcm_channels
+        c.init_channels, c.growth, c.bn_size, c.n_blocks = cfg.init_channels, cfg.growth, cfg.bn_size, len(cfg.block_layers)
+        for i, (nl, k, d) in enumerate(zip(cfg.block_layers, cfg.block_kernel, cfg.block_dilation)):
+            c.layers[i], c.kernel[i], c.dilation[i] = nl, k, d
+        c.seg_len, c.bn_eps = cfg.seg_len, cfg.bn_eps
+        check(self.lib.fy_load_campplus(self.h, arr, len(state), C.byref(c)))
 
     def load_s3tok(self, state: dict, cfg):
         arr, keep = self._tensor_table(state)

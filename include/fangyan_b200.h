@@ -55,6 +55,14 @@ typedef struct {
   float rope_theta, ln_eps, fsq_scale;
 } fy_s3_config;
 
+/* Hyper-parameters of CAMPPlus (UNVERIFIED against the real ONNX graph). */
+typedef struct {
+  int32_t feat_dim, embed_dim, fcm_channels, init_channels, growth, bn_size, n_blocks;
+  int32_t layers[4], kernel[4], dilation[4];
+  int32_t seg_len;
+  float bn_eps;
+} fy_campplus_config;
+
 /* ---- lifetime ------------------------------------------------------------------------------------------- */
 int fy_create(int device, int precision, fy_ctx** out);
 void fy_destroy(fy_ctx* ctx);
@@ -65,7 +73,7 @@ const char* fy_version(void);
 /* ---- weights: replaces onnxruntime.InferenceSession(onnx_path) ---------------------------------------------
  * tools/extract_embedding.py:94, tools/extract_speech_token.py:90, cosyvoice/cli/frontend.py:45-48.
  * BatchNorm folding, bf16 hi/lo splitting and conv-weight re-layout happen here, once. */
-int fy_load_campplus(fy_ctx* ctx, const fy_tensor* h_tensors, int n);
+int fy_load_campplus(fy_ctx* ctx, const fy_tensor* h_tensors, int n, const fy_campplus_config* cfg);
 int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* h_tensors, int n, const fy_s3_config* cfg);
 
 /* ---- A2: torchaudio.transforms.Resample(orig, 16000) ------------------------------------------------------
