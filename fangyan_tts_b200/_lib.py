@@ -40,6 +40,7 @@ PROTOTYPES = {
     "fy_logmel": (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _P, _P, _Z]),
     "fy_campplus_workspace_bytes": (_Z, [_P, _I, _I]),
     "fy_campplus_forward": (_I, [_P, _P, _P, _P, _I, _P, _P, _Z]),
+    "fy_campplus_layout": (_I, [_P, _P, _I, _P, _I]),
     "fy_s3tok_workspace_bytes": (_Z, [_P, _I, _I]),
     "fy_s3tok_encode_fsq": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _P, _Z]),
     "fy_speaker_sum": (_I, [_P, _P, _P, _I, _I, _P, _P]),

@@ -56,12 +56,12 @@ __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ fea
   *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8) = o;
 }
 
-// mask[g] = time row (g / Q) valid and lo <= g % Q <= hi ? 0 : -1
+// mask[g] = -2 (skip) when slot g % Q is outside [lo, hi]; else -1 (write zero) on guard time rows; else 0
 __global__ void pos_mask_kernel(const int* __restrict__ rowsrc, int R, int Q, int lo, int hi, int* __restrict__ mask) {
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= R * Q) return;
   const int p = g % Q;
-  mask[g] = (rowsrc[g / Q] >= 0 && p >= lo && p <= hi) ? 0 : -1;
+  mask[g] = (p < lo || p > hi) ? -2 : (rowsrc[g / Q] >= 0 ? 0 : -1);
 }
 
 // y = bf16(relu(x * scale[c] + shift[c])) for c < C; x fp32 [R, ldx], y bf16 [R, ldy].  4 channels per thread.

@@ -478,3 +478,26 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }
+
+// Debug / test aid: byte offsets of the activation buffers inside the workspace for a given batch.
+// out: [R50, R100, x0, y40, s40, z40a, z40b, y20, s20, z20a, z20b, fcm, cat0, cat1, cat2, cat3, hin, hb, gate, stats]
+extern "C" int fy_campplus_layout(fy_ctx* ctx, const int32_t* h_frame_off, int n_utts, int64_t* out, int n_out) {
+  FY_CHECK(ctx && h_frame_off && out && n_out >= 20, FY_ERR_ARG, "fy_campplus_layout: bad argument");
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  CamPlan* p = reinterpret_cast<CamPlan*>(c->cam_plan);
+  FY_CHECK(p != nullptr, FY_ERR_STATE, "fy_campplus_layout: call fy_load_campplus first");
+  int row = 0, nseg = 0;
+  for (int u = 0; u < n_utts; ++u) {
+    const int T = h_frame_off[u + 1] - h_frame_off[u];
+    const int t2 = (T - 1) / 2 + 1;
+    row += t2 + 2;
+    nseg += (t2 + p->cfg.seg_len - 1) / p->cfg.seg_len;
+  }
+  Layout l = make_layout(p, n_utts, row, nseg);
+  const int64_t v[20] = {l.R50, l.R100, (int64_t)l.o_x0, (int64_t)l.o_y40, (int64_t)l.o_s40, (int64_t)l.o_z40a,
+                         (int64_t)l.o_z40b, (int64_t)l.o_y20, (int64_t)l.o_s20, (int64_t)l.o_z20a, (int64_t)l.o_z20b,
+                         (int64_t)l.o_fcm, (int64_t)l.o_cat[0], (int64_t)l.o_cat[1], (int64_t)l.o_cat[2],
+                         (int64_t)l.o_cat[3], (int64_t)l.o_hin, (int64_t)l.o_hb, (int64_t)l.o_gate, (int64_t)l.o_stats};
+  for (int i = 0; i < 20; ++i) out[i] = v[i];
+  return FY_OK;
+}

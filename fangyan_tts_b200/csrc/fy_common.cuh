@@ -57,7 +57,7 @@ struct GemmEpi {
   int lo_col_off = -1;   // EPI_BF16 only: if >= 0 also write the bf16 residual (x - bf16(x)) at this column offset
   const float* scale = nullptr;    // [N] per-column multiplier (folded BatchNorm) or null
   const float* bias = nullptr;     // [N] per-column addend or null
-  const int* row_idx = nullptr;    // [M] or null: rows with row_idx < 0 are written as zero
+  const int* row_idx = nullptr;    // [M] or null: row_idx == -1 -> row written as zero; -2 -> row not written
   const float* row_gate = nullptr; // [*, N] or null: multiply by row_gate[row_idx[row] * N + n] (CAM mask)
   const __nv_bfloat16* resid = nullptr;  // EPI_BF16 only: bf16 tensor (same rows / ldo / col_off as out) added before act
   // output row remap: out_row = (row / remap_q) * remap_fp + row % remap_q + remap_add   (remap_q == 0: identity)

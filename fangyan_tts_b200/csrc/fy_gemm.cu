@@ -157,9 +157,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       }
       asm volatile("bar.sync 1, 128;\n" ::: "memory");
       const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < args.M;
+      bool row_ok = row < args.M;
       int ridx = 0;
       if (e.row_idx) ridx = row_ok ? __ldg(e.row_idx + row) : -1;
+      if (ridx == -2) row_ok = false;  // -2: leave the output row untouched; -1: write zeros
       const bool keep = ridx >= 0;
       const size_t orow = e.remap_q ? (size_t)(row / e.remap_q) * e.remap_fp + row % e.remap_q + e.remap_add : (size_t)row;
       ptx::mbar_wait(&tfull_bar[as], aphase);

@@ -108,6 +108,9 @@ size_t fy_campplus_workspace_bytes(fy_ctx* ctx, int n_utts, int total_frames);
 int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t* frame_off, const int32_t* h_frame_off,
                         int n_utts, float* emb, void* ws, size_t ws_bytes);
 
+/* Test aid: byte offsets of CAMPPlus activation buffers inside the workspace (see fy_campplus.cu). */
+int fy_campplus_layout(fy_ctx* ctx, const int32_t* h_frame_off, int n_utts, int64_t* out, int n_out);
+
 /* ---- A9 + A10: ort_session.run(None, {feat, feat_len}) on speech_tokenizer_v3.onnx ------------------------
  * tools/extract_speech_token.py:40-48, cosyvoice/cli/frontend.py:99-103.
  * mel: packed as written by fy_logmel.  tokens: packed int32, L_b = ((T_b - 1) / 2 + 1 - 1) / 2 + 1 per utterance;

@@ -15,7 +15,7 @@ def test_campplus_matches_oracle(engine):
     cfg = CP.CamPlusConfig()
     model = CP.init_random(CP.CamPlus(cfg), seed=1986)
     engine.load_campplus(dict(model.state_dict()), cfg)
-    utts = synth.make_set(7, 21, 0.6, 7.0) + [synth.make_set(1, 5, 0.03, 0.035)[0], synth.make_set(1, 6, 20.0, 21.0)[0]]
+    utts = synth.make_set(7, 21, 0.6, 7.0) + [synth.make_set(1, 5, 0.065, 0.07)[0], synth.make_set(1, 6, 20.0, 21.0)[0]]
     feats = [F.cmn(F.kaldi_fbank(torch.from_numpy(u.astype(np.float32) / 32768.0)[None])) for u in utts]
     frames = [f.shape[0] for f in feats]
     emb = engine.campplus(torch.cat(feats).cuda(), frames).cpu()
