@@ -1,0 +1,315 @@
+#!/usr/bin/env python3
+"""Benchmark of the stage 1+2 extraction hot path (BASELINE.json metric: audio-hours/sec).
+
+A "step" is one pass of stage 1 (fbank+CMN -> CAMPPlus -> speaker mean) and stage 2 (log-mel -> S3 encoder -> FSQ)
+over a fixed set of synthetic utterances (default 1,000 utterances of 3-10 s, the size of BASELINE configs[1];
+configs[2]'s 1,000 hours is this step repeated).  `value` times the step with PCM already resident in HBM;
+`e2e` times it through the public API (fangyan_tts_b200.pipeline.Extractor) from pinned host PCM to host results.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "audio_hours_per_sec_stage1+2"
+UNIT = "audio-hours/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--utts", type=int, default=int(os.environ.get("FY_BENCH_UTTS", "1000")))
+    ap.add_argument("--precision", default=os.environ.get("FY_PRECISION", "bf16x3"), choices=["bf16", "bf16x3"])
+    ap.add_argument("--batch-seconds", type=float, default=float(os.environ.get("FY_BATCH_SECONDS", "2400")))
+    ap.add_argument("--cpu-sample", type=int, default=6, help="utterances in the bounded CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload(n_utts: int, seed: int):
+    """Seeded synthetic utterances: a pool of distinct waveforms, cut to U(3, 10) s lengths."""
+    from fangyan_tts_b200 import synth
+    rng = np.random.default_rng(seed)
+    pool = [synth.utterance(rng, 10.0) for _ in range(min(n_utts, 48))]
+    utts = []
+    for i in range(n_utts):
+        n = int(rng.uniform(3.0, 10.0) * 16000)
+        base = pool[i % len(pool)]
+        off = int(rng.integers(0, len(base) - n + 1))
+        utts.append(np.ascontiguousarray(base[off:off + n]))
+    return utts
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops", 1590.0), d.get("bf16_tflops_sustained", 1400.0), "measured"
+    return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = sorted(sm)[len(sm) // 2:] if sm else []
+        return {"sm_mhz": float(np.median(busy)) if busy else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+
+
+def cpu_reference_rate(utts, threads: int):
+    """The reference's per-utterance path restated on the CPU (oracle/; torch fp32, batch 1, true length):
+    returns (audio-hours/s, audio seconds processed, wall seconds)."""
+    import torch
+    from oracle import campplus as CP, frontend as F, s3tokenizer as S3
+    torch.set_num_threads(threads)
+    cam = CP.init_random(CP.CamPlus())
+    s3 = S3.init_random(S3.S3Tokenizer())
+    t0 = time.perf_counter()
+    secs = 0.0
+    for u in utts:
+        x = torch.from_numpy(u.astype(np.float32) / 32768.0)[None]
+        CP.embed_one(cam, F.cmn(F.kaldi_fbank(x)))
+        if F.stage2_gate(x.shape[1]):
+            S3.tokenize_one(s3, F.whisper_log_mel(x))
+        secs += len(u) / 16000.0
+    wall = time.perf_counter() - t0
+    return secs / 3600.0 / wall, secs, wall
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from fangyan_tts_b200.engine import Engine
+    from fangyan_tts_b200.pipeline import Extractor, Utt, plan_batches
+    from oracle import campplus as CP, s3tokenizer as S3  # weights only: random-init state dicts of the named nets
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = Engine(local, args.precision)
+    cam_cfg, s3_cfg = CP.CamPlusConfig(), S3.S3Config()
+    eng.load_campplus(dict(CP.init_random(CP.CamPlus(cam_cfg)).state_dict()), cam_cfg)
+    s3 = S3.init_random(S3.S3Tokenizer(s3_cfg))
+    st = dict(s3.state_dict())
+    st["rope.cos"], st["rope.sin"] = S3.rope_tables(2048, s3_cfg.d_head, s3_cfg.rope_theta)
+    eng.load_s3tok(st, s3_cfg)
+    del s3, st
+
+    utts = workload(args.utts, 1986 + 2 + rank)          # weak scaling: every rank owns its own shard
+    audio_s = sum(len(u) for u in utts) / 16000.0
+    n_spk = 11
+    dur = [len(u) / 16000.0 for u in utts]
+    batches = plan_batches(dur, args.batch_seconds, 4096)
+    dev = eng.device
+    resident = []
+    for idx in batches:
+        pcm = torch.from_numpy(np.concatenate([utts[i] for i in idx])).to(dev)
+        spk = torch.tensor([i % n_spk for i in idx], dtype=torch.int32, device=dev)
+        resident.append((pcm, [len(utts[i]) for i in idx], spk))
+    ssum = torch.zeros(n_spk, 192, device=dev)
+    scnt = torch.zeros(n_spk, dtype=torch.int32, device=dev)
+
+    def step_device():
+        ssum.zero_()
+        scnt.zero_()
+        out = None
+        for pcm, lens, spk in resident:
+            feat, frames = eng.fbank_cmn(pcm, lens)
+            emb = eng.campplus(feat, frames)
+            eng.speaker_sum(emb, spk, n_spk, ssum, scnt)
+            mel, mframes = eng.logmel(pcm, lens)
+            tok, counts = eng.s3tok(mel, mframes)
+            out = (emb, tok)
+        return eng.speaker_mean(ssum, scnt), out
+
+    ex = Extractor(eng, max_batch_seconds=args.batch_seconds, max_batch_utts=4096)
+    host_utts = [Utt(u.reshape(-1, 1), 16000) for u in utts]
+    h2d = sum(len(u) for u in utts) * 2
+    d2h = [0]
+
+    def step_e2e():
+        emb = ex.embed(host_utts)
+        toks = ex.tokenize(host_utts)
+        d2h[0] = emb.nbytes + sum(len(t) for t in toks) * 4
+        return emb, toks
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            fn()
+        b.record()
+        barrier()
+        ms = a.elapsed_time(b)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    prof = (C.c_double * 10)()
+    eng.lib.fy_profile_read(eng.h, prof, 10)          # clear counters
+    eng.lib.fy_profile_enable(eng.h, 1)
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms = timed(step_device, args.steps)
+    clk = clocks.stop() if rank == 0 else None
+    eng.lib.fy_profile_read(eng.h, prof, 10)
+    eng.lib.fy_profile_enable(eng.h, 0)
+    p = list(prof)
+
+    step_e2e()                                            # warm the pinned buffers
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 3))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    hbm, tf_burst, tf_sust, which = peaks()
+    ms_per_step = ms / args.steps
+    value = world * audio_s / 3600.0 / (ms_per_step / 1e3)
+    gemm_ms, gemm_flops, gemm_n = p[0], p[3], p[6]
+    achieved = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16x3 (split-bf16 tensor-core products, fp32 accumulate)" if args.precision == "bf16x3" else "bf16",
+        "data": "synthetic",
+        "config": {"workload": f"stage1+2 over {args.utts} synthetic 16 kHz utterances of 3-10 s per GPU "
+                               f"({audio_s / 3600.0:.3f} audio-hours; BASELINE configs[1] size, both stages)",
+                   "batches_per_step": len(batches), "batch_seconds": args.batch_seconds,
+                   "weights": "random-init CAMPPlus + S3 tokenizer v3 (12 layers)", "precision": args.precision,
+                   "l2": "per-step inputs and workspaces (GBs) exceed the 126 MB L2", "parallelism": f"dp{world}"},
+        "e2e": {"value": world * audio_s / 3600.0 / (e2e_s / e2e_steps), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h[0], "steps": e2e_steps},
+        "gpu_launches": int(p[9]),
+        "roofline": {"bound": "tensor", "kernel": "gemm_kernel<BN> (tcgen05)", "achieved": achieved, "peak": tf_sust,
+                     "unit": "TFLOP/s", "frac": achieved / tf_sust, "traffic": None, "peak_source": f"{which} sustained",
+                     "launches": int(gemm_n), "avg_launch_ms": gemm_ms / max(gemm_n, 1),
+                     "gemm_share_of_step": gemm_ms / ms, "attention_ms_per_step": p[1] / args.steps},
+        "clocks": clk,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        threads = len(os.sched_getaffinity(0))
+        sample = utts[:args.cpu_sample]
+        v, secs, wall = cpu_reference_rate(sample, threads)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"first {len(sample)} utterances of the workload ({secs:.1f} audio-s, {wall:.1f} s wall), "
+                                          "oracle = torch-cpu restatement (onnxruntime unavailable)"}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = len(os.sched_getaffinity(0))
+    utts = workload(args.utts, 1986 + 2)
+    sample = utts[:args.cpu_sample]
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_rate(sample[:1], threads)
+    rates, wall_tot = [], 0.0
+    for _ in range(max(1, min(args.steps, 3))):
+        v, secs, wall = cpu_reference_rate(sample, threads)
+        rates.append(v)
+        wall_tot += wall
+    v = float(np.median(rates))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * wall_tot / len(rates), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"stage1+2, bounded sample: first {len(sample)} of {args.utts} synthetic utterances, "
+                               "batch 1 at true length as the reference does"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{len(sample)} utterances per step; torch-cpu restatement of the reference path "
+                                   "(onnxruntime / whisper / the .onnx files are not installable offline)"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

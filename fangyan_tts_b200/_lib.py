@@ -45,6 +45,8 @@ PROTOTYPES = {
     "fy_s3tok_encode_fsq": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _P, _Z]),
     "fy_speaker_sum": (_I, [_P, _P, _P, _I, _I, _P, _P]),
     "fy_speaker_mean_finish": (_I, [_P, _P, _P, _I, _P]),
+    "fy_profile_enable": (_I, [_P, _I]),
+    "fy_profile_read": (_I, [_P, C.POINTER(C.c_double), _I]),
     "fy_gemm_bf16": (_I, [_P, _P, _P, _P, _I, _I, _I]),
 }
 

@@ -20,6 +20,29 @@ int frontend_init(Ctx* c);   // fy_frontend.cu
 void s3_free_plan(Ctx* c);   // fy_s3tok.cu
 void cam_free_plan(Ctx* c);  // fy_campplus.cu
 
+int prof_begin(Ctx* c, int kind) {
+  if (!c->prof) return -1;
+  Ctx::ProfRec r;
+  r.kind = kind;
+  r.flops = 0;
+  if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) return -1;
+  cudaEventRecord(r.a, c->stream);
+  c->recs.push_back(r);
+  return (int)c->recs.size() - 1;
+}
+void prof_end(Ctx* c, int idx, double flops) {
+  if (idx < 0) return;
+  c->recs[idx].flops = flops;
+  cudaEventRecord(c->recs[idx].b, c->stream);
+}
+int run_gemm(Ctx* c, const GemmArgs& g, double alg_flops) {
+  const int pi = prof_begin(c, PK_GEMM);
+  const int r = launch_gemm(g, c->num_sms, c->stream);
+  prof_end(c, pi, alg_flops);
+  c->launches += 1;
+  return r;
+}
+
 namespace {
 
 __global__ void speaker_sum_kernel(const float* __restrict__ emb, const int* __restrict__ spk, int n_utts, int n_spk,
@@ -101,6 +124,34 @@ int fy_set_stream(fy_ctx* ctx, void* cuda_stream) {
   return FY_OK;
 }
 
+int fy_profile_enable(fy_ctx* ctx, int on) {
+  FY_CHECK(ctx != nullptr, FY_ERR_ARG, "fy_profile_enable: ctx is NULL");
+  reinterpret_cast<Ctx*>(ctx)->prof = on != 0;
+  return FY_OK;
+}
+
+// out[0..2] = ms per kind (gemm, attention, other), out[3..5] = algorithmic FLOPs per kind,
+// out[6..8] = timed launches per kind, out[9] = all kernel launches since the last read.  Synchronises the stream.
+int fy_profile_read(fy_ctx* ctx, double* out, int n_out) {
+  FY_CHECK(ctx && out && n_out >= 10, FY_ERR_ARG, "fy_profile_read: bad argument");
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  FY_CUDA(cudaStreamSynchronize(c->stream));
+  for (int i = 0; i < 10; ++i) out[i] = 0.0;
+  for (auto& r : c->recs) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    out[r.kind] += ms;
+    out[3 + r.kind] += r.flops;
+    out[6 + r.kind] += 1.0;
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  c->recs.clear();
+  out[9] = (double)c->launches;
+  c->launches = 0;
+  return FY_OK;
+}
+
 int fy_gemm_bf16(fy_ctx* ctx, const void* a, const void* b, float* out, int M, int N, int K) {
   FY_CHECK(ctx && a && b && out, FY_ERR_ARG, "fy_gemm_bf16: NULL argument");
   FY_CHECK(M > 0 && N > 0 && K > 0 && K % 8 == 0 && N % 32 == 0, FY_ERR_ARG,
@@ -116,7 +167,7 @@ int fy_gemm_bf16(fy_ctx* ctx, const void* a, const void* b, float* out, int M, i
   g.epi.mode = EPI_F32_STORE;
   g.epi.out = out;
   g.epi.ldo = N;
-  return launch_gemm(g, c->num_sms, c->stream);
+  return run_gemm(c, g, 2.0 * M * N * K);
 }
 
 int fy_speaker_sum(fy_ctx* ctx, const float* emb, const int32_t* spk_id, int n_utts, int n_spk, float* sum,

@@ -285,7 +285,7 @@ struct FcmConv {
   const int* mask; const __nv_bfloat16* resid; bool relu;
 };
 
-int run_fcm_conv(Ctx* c, const FcmConv& f, int R100) {
+int run_fcm_conv(Ctx* c, const FcmConv& f, int R100, double vframes) {
   GemmArgs g;
   g.N = 32;
   g.tmap_b = f.w->map;
@@ -316,7 +316,8 @@ int run_fcm_conv(Ctx* c, const FcmConv& f, int R100) {
   g.epi.row_idx = f.mask;
   g.epi.resid = f.resid;
   if (f.stride2 || f.out_fp != Q) { g.epi.remap_q = Q; g.epi.remap_fp = f.out_fp; g.epi.remap_add = f.out_add; }
-  return launch_gemm(g, c->num_sms, c->stream);
+  const int fout = f.stride2 ? Q - 1 : Q - 2;
+  return run_gemm(c, g, 2.0 * vframes * fout * 32 * (f.k3 ? 288 : 32));
 }
 
 }  // namespace
@@ -336,6 +337,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   // ---- plan
   std::vector<int> B(n_utts), T2(n_utts), SB(n_utts);
   int row = 0, nseg = 0;
+  double vT = 0, vT2 = 0;  // valid frames at 100 / 50 Hz, for algorithmic FLOP accounting
   for (int u = 0; u < n_utts; ++u) {
     const int T = h_frame_off[u + 1] - h_frame_off[u];
     FY_CHECK(T >= 3, FY_ERR_ARG, "fy_campplus_forward: utterance %d has %d frames (need >= 3)", u, T);
@@ -343,6 +345,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
     const int ns = (T2[u] + cf.seg_len - 1) / cf.seg_len;
     FY_CHECK(ns <= camk::kMaxSegPerUtt, FY_ERR_ARG, "fy_campplus_forward: utterance %d too long (%d frames)", u, T);
     B[u] = row; SB[u] = nseg;
+    vT += T; vT2 += T2[u];
     row += T2[u] + 2;
     nseg += ns;
   }
@@ -394,13 +397,13 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
       const Stage& S = stg[s];
       const ResW& r0 = p->res[2 * s];
       const ResW& r1 = p->res[2 * s + 1];
-      FY_TRY(run_fcm_conv(c, FcmConv{&r0.c1, S.in, S.in_fp, true, true, S.y, S.fp, 1, S.ms, nullptr, true}, R100));
-      FY_TRY(run_fcm_conv(c, FcmConv{&r0.sc, S.in, S.in_fp, true, false, S.s, S.fp, 1, S.ms, nullptr, false}, R100));
-      FY_TRY(run_fcm_conv(c, FcmConv{&r0.c2, S.y, S.fp, false, true, S.za, S.fp, 0, S.m, S.s, true}, R100));
-      FY_TRY(run_fcm_conv(c, FcmConv{&r1.c1, S.za, S.fp, false, true, S.y, S.fp, 0, S.m, nullptr, true}, R100));
-      FY_TRY(run_fcm_conv(c, FcmConv{&r1.c2, S.y, S.fp, false, true, S.zb, S.fp, 0, S.m, S.za, true}, R100));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r0.c1, S.in, S.in_fp, true, true, S.y, S.fp, 1, S.ms, nullptr, true}, R100, vT));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r0.sc, S.in, S.in_fp, true, false, S.s, S.fp, 1, S.ms, nullptr, false}, R100, vT));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r0.c2, S.y, S.fp, false, true, S.za, S.fp, 0, S.m, S.s, true}, R100, vT));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r1.c1, S.za, S.fp, false, true, S.y, S.fp, 0, S.m, nullptr, true}, R100, vT));
+      FY_TRY(run_fcm_conv(c, FcmConv{&r1.c2, S.y, S.fp, false, true, S.zb, S.fp, 0, S.m, S.za, true}, R100, vT));
     }
-    FY_TRY(run_fcm_conv(c, FcmConv{&p->fcm_out, H(lay.o_z20b), 22, true, true, H(lay.o_fcm), 10, 0, m11s, nullptr, true}, R100));
+    FY_TRY(run_fcm_conv(c, FcmConv{&p->fcm_out, H(lay.o_z20b), 22, true, true, H(lay.o_fcm), 10, 0, m11s, nullptr, true}, R100, vT));
   }
   // ---- TDNN: Conv1d(320 -> 128, k5, stride 2, pad 2) + BN + ReLU -> concat block 0, columns [0, 128)
   int ctot[4];
@@ -419,7 +422,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
     g.seg[g.nseg++] = GemmSeg{2, 0, 1280, 5};
     g.epi.mode = EPI_F32_STORE; g.epi.act = ACT_RELU; g.epi.out = Fp(lay.o_cat[0]); g.epi.ldo = ctot[0];
     g.epi.scale = p->tdnn_bn.scale; g.epi.bias = p->tdnn_bn.shift; g.epi.row_idx = d_rowseg;
-    FY_TRY(launch_gemm(g, c->num_sms, st));
+    FY_TRY(run_gemm(c, g, 2.0 * vT2 * 128 * 1600));
   }
   // ---- dense blocks
   __nv_bfloat16* hin = H(lay.o_hin);
@@ -444,8 +447,9 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
         g.seg[g.nseg++] = GemmSeg{0, 0, 0, (d.cin + 63) / 64};
         g.epi.mode = EPI_BF16; g.epi.act = ACT_RELU; g.epi.out = hb; g.epi.ldo = 128;
         g.epi.scale = d.bn2.scale; g.epi.bias = d.bn2.shift; g.epi.row_idx = d_rowseg;
-        FY_TRY(launch_gemm(g, c->num_sms, st));
+        FY_TRY(run_gemm(c, g, 2.0 * vT2 * 128 * d.cin));
       }
+      c->launches += 2;  // bnrelu, cam_gate
       camk::cam_gate_kernel<<<n_utts, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
       {
         GemmArgs g;
@@ -453,7 +457,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
         for (int k = 0; k < 3; ++k) g.seg[g.nseg++] = GemmSeg{(k - 1) * dil, 0, k * 128, 2};
         g.epi.mode = EPI_F32_STORE; g.epi.out = cat; g.epi.ldo = ld; g.epi.col_off = d.cin;
         g.epi.row_idx = d_rowseg; g.epi.row_gate = gate;
-        FY_TRY(launch_gemm(g, c->num_sms, st));
+        FY_TRY(run_gemm(c, g, 2.0 * vT2 * 32 * 384));
       }
     }
     const TransW& tr = p->trans[b];
@@ -466,12 +470,13 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
       g.seg[g.nseg++] = GemmSeg{0, 0, 0, (tr.cin + 63) / 64};
       g.epi.mode = EPI_F32_STORE; g.epi.out = Fp(lay.o_cat[b + 1]); g.epi.ldo = ctot[b + 1];
       g.epi.row_idx = d_rowseg;
-      FY_TRY(launch_gemm(g, c->num_sms, st));
+      FY_TRY(run_gemm(c, g, 2.0 * vT2 * tr.cout * tr.cin));
     }
   }
   // ---- BN + ReLU -> statistics pooling -> dense -> BN
   const int C = ctot[cf.n_blocks];
   float* stats = Fp(lay.o_stats);
+  c->launches += 12;  // memset, 5 masks, stem, 3 transit bnrelu, stats, dense
   camk::stats_kernel<<<n_utts, 512, 0, st>>>(Fp(lay.o_cat[cf.n_blocks]), C, C, d_B, d_T2, p->out_bn.scale, p->out_bn.shift, stats);
   camk::dense_kernel<<<n_utts, 256, 2 * C * 4, st>>>(stats, 2 * C, cf.embed_dim, p->dense_w, p->dense_bn.scale,
                                                      p->dense_bn.shift, emb);

@@ -110,6 +110,16 @@ struct Ctx {
   void* s3_plan = nullptr;
   std::map<std::pair<int, int>, float*> resample_kern;  // (orig, new) reduced -> device filter bank
   std::vector<void*> owned;        // misc device allocations freed in destroy
+  // optional per-kernel-class timing (fy_profile_*): CUDA events recorded on the launch stream
+  struct ProfRec { int kind; double flops; cudaEvent_t a, b; };
+  bool prof = false;
+  std::vector<ProfRec> recs;
+  long long launches = 0;          // kernels launched since the last fy_profile_read
 };
+
+enum ProfKind { PK_GEMM = 0, PK_ATTN = 1, PK_OTHER = 2, PK_COUNT = 3 };
+int prof_begin(Ctx* c, int kind);                 // returns a record index or -1 when profiling is off
+void prof_end(Ctx* c, int idx, double flops);
+int run_gemm(Ctx* c, const GemmArgs& g, double alg_flops);  // launch_gemm + launch counting + profiling
 
 }  // namespace fy

@@ -472,6 +472,7 @@ int launch_fbank(Ctx* c, const void* pcm, int dtype, const int* pcm_off, const i
                                                                     c->fb_window, c->fb_tw, mt, feat);
   FY_CUDA(cudaGetLastError());
   cmn_kernel<<<n_utts, 320, 0, c->stream>>>(feat, frame_off);
+  c->launches += 2;
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }
@@ -532,6 +533,7 @@ int fy_logmel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_of
   FY_TRY(launch_logmel_raw(c, pcm, pcm_dtype, pcm_off, frame_off, n_utts, total_frames, raw, umax));
   dim3 grid((max_frames + 31) / 32, n_utts);
   logmel_finish_kernel<<<grid, 256, 0, c->stream>>>(raw, frame_off, umax, mel);
+  c->launches += 3;
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }

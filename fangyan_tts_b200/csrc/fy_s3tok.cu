@@ -306,6 +306,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   // ---- plan the packed layout on the host
   std::vector<int> P(n_utts), L(n_utts);
   int row = 0, tiles = 0, Tmax = 0;
+  double vtok = 0, vc1 = 0, attn_flops = 0;  // valid rows, for algorithmic FLOP accounting
   for (int u = 0; u < n_utts; ++u) {
     const int T = h_frame_off[u + 1] - h_frame_off[u];
     FY_CHECK(T > 0, FY_ERR_ARG, "fy_s3tok_encode_fsq: utterance %d has %d mel frames", u, T);
@@ -313,6 +314,9 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
     L[u] = token_len(T);
     FY_CHECK(L[u] <= p->rope_len, FY_ERR_ARG, "utterance %d has %d tokens, rope table holds %d", u, L[u], p->rope_len);
     row += L[u] + 1;
+    vtok += L[u];
+    vc1 += (T - 1) / 2 + 1;
+    attn_flops += 4.0 * L[u] * L[u] * D;
     tiles += (L[u] + 63) / 64;
     Tmax = std::max(Tmax, T);
   }
@@ -390,7 +394,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       add_products(g, W, tap / 2, (tap % 2) * rw, tap * NM, NM, NM, 3 * NM);
     g.epi.mode = EPI_BF16; g.epi.act = ACT_GELU; g.epi.out = b_c1; g.epi.ldo = D * W;
     g.epi.lo_col_off = W == 2 ? D : -1; g.epi.bias = p->bc1; g.epi.row_idx = d_row1;
-    FY_TRY(launch_gemm(g, c->num_sms, st));
+    FY_TRY(run_gemm(c, g, 2.0 * vc1 * D * 3 * NM));
   }
   // ---- conv2: [Rtok, 3*D] x [D, 3*D]^T, bias + GELU, masked rows -> x (fp32)
   {
@@ -403,7 +407,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       add_products(g, W, tap / 2, (tap % 2) * rw, tap * D, D, D, 3 * D);
     g.epi.mode = EPI_F32_STORE; g.epi.act = ACT_GELU; g.epi.out = b_x; g.epi.ldo = D;
     g.epi.bias = p->bc2; g.epi.row_idx = d_rutt;
-    FY_TRY(launch_gemm(g, c->num_sms, st));
+    FY_TRY(run_gemm(c, g, 2.0 * vtok * D * 3 * D));
   }
   // ---- A-side tensor maps shared by all layers
   CUtensorMap m_xn, m_att, m_h;
@@ -422,7 +426,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       g.tmap_a = m_xn; g.tmap_b = Lw.m_qkv; g.M = Rtok; g.N = 3 * D;
       add_products(g, W, 0, 0, 0, D, D, D);
       g.epi.mode = EPI_F32_STORE; g.epi.out = b_qkv; g.epi.ldo = 3 * D; g.epi.bias = Lw.bqkv;
-      FY_TRY(launch_gemm(g, c->num_sms, st));
+      FY_TRY(run_gemm(c, g, 2.0 * vtok * 3 * D * D));
     }
     {
       const size_t n = (size_t)Rtok * (D / 2);
@@ -435,9 +439,12 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       s3k::fsmn_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(b_qkv, d_rutt, d_rpos, d_L, Lw.fsmn, Rtok, D, cf.fsmn_kernel, b_x);
     }
     {
+      const int pi = prof_begin(c, PK_ATTN);
       dim3 grid(tiles, cf.n_head);
       if (W == 2) attn::attention_kernel<true><<<grid, attn::kThreads, attn::smem_bytes<true>(), st>>>(b_q, b_k, b_v, b_att, D * W, D, d_tiles, d_P, d_L);
       else attn::attention_kernel<false><<<grid, attn::kThreads, attn::smem_bytes<false>(), st>>>(b_q, b_k, b_v, b_att, D * W, D, d_tiles, d_P, d_L);
+      prof_end(c, pi, attn_flops);
+      c->launches += 5;  // layernorm x2, rope, fsmn, attention
     }
     FY_CUDA(cudaGetLastError());
     {
@@ -445,7 +452,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       g.tmap_a = m_att; g.tmap_b = Lw.m_o; g.M = Rtok; g.N = D;
       add_products(g, W, 0, 0, 0, D, D, D);
       g.epi.mode = EPI_F32_ADD; g.epi.out = b_x; g.epi.ldo = D; g.epi.bias = Lw.bo;
-      FY_TRY(launch_gemm(g, c->num_sms, st));
+      FY_TRY(run_gemm(c, g, 2.0 * vtok * D * D));
     }
     if (W == 2) s3k::layernorm_kernel<true, 1280><<<ln_grid, 256, 0, st>>>(b_x, Lw.ln2_g, Lw.ln2_b, cf.ln_eps, Rtok, b_xn);
     else s3k::layernorm_kernel<false, 1280><<<ln_grid, 256, 0, st>>>(b_x, Lw.ln2_g, Lw.ln2_b, cf.ln_eps, Rtok, b_xn);
@@ -455,16 +462,17 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       add_products(g, W, 0, 0, 0, D, D, D);
       g.epi.mode = EPI_BF16; g.epi.act = ACT_GELU; g.epi.out = b_h; g.epi.ldo = F * W;
       g.epi.lo_col_off = W == 2 ? F : -1; g.epi.bias = Lw.b1;
-      FY_TRY(launch_gemm(g, c->num_sms, st));
+      FY_TRY(run_gemm(c, g, 2.0 * vtok * F * D));
     }
     {
       GemmArgs g;
       g.tmap_a = m_h; g.tmap_b = Lw.m_2; g.M = Rtok; g.N = D;
       add_products(g, W, 0, 0, 0, F, F, F);
       g.epi.mode = EPI_F32_ADD; g.epi.out = b_x; g.epi.ldo = D; g.epi.bias = Lw.b2;
-      FY_TRY(launch_gemm(g, c->num_sms, st));
+      FY_TRY(run_gemm(c, g, 2.0 * vtok * D * F));
     }
   }
+  c->launches += 3;  // memset, mel_to_rows, fsq
   s3k::fsq_kernel<<<(Rtok + 7) / 8, 256, 0, st>>>(b_x, d_rutt, d_rpos, tok_off, p->pd_w, p->pd_b, Rtok, D, cf.fsq_scale,
                                                  tokens, fsq_pre);
   FY_CUDA(cudaGetLastError());

@@ -128,6 +128,12 @@ int fy_speaker_sum(fy_ctx* ctx, const float* emb, const int32_t* spk_id, int n_u
                    int32_t* count);
 int fy_speaker_mean_finish(fy_ctx* ctx, const float* sum, const int32_t* count, int n_spk, float* mean);
 
+/* ---- measurement aid: CUDA-event timing per kernel class on the launch stream ----------------------------
+ * out[0..2] ms (tcgen05 GEMM, attention, other), out[3..5] algorithmic FLOPs, out[6..8] timed launches,
+ * out[9] all kernel launches since the previous read.  fy_profile_read synchronises the stream. */
+int fy_profile_enable(fy_ctx* ctx, int on);
+int fy_profile_read(fy_ctx* ctx, double* out, int n_out);
+
 /* ---- generic bf16 tensor-core GEMM (exposed for tests and tuning) -----------------------------------------
  * out[M, N] (fp32) = A[M, K] * B[N, K]^T with A, B bf16 row-major. */
 int fy_gemm_bf16(fy_ctx* ctx, const void* a_bf16, const void* b_bf16, float* out, int M, int N, int K);
