@@ -81,49 +81,56 @@ __global__ void __launch_bounds__(256) bnrelu_kernel(const float* __restrict__ x
   *reinterpret_cast<uint2*>(y + (size_t)r * ldy + c) = o;
 }
 
-// CAM gate.  h: bf16 [R50, 128] (post BN+ReLU bottleneck).  For utterance u (rows B_u .. B_u + T_u):
-//   ctx[s] = mean over all rows + mean over rows of segment s (seg_len rows, last one partial)
-//   gate[seg_base_u + s][0..32) = sigmoid(W2 relu(W1 ctx + b1) + b2)
-// One block of 128 threads per utterance; supports up to kMaxSeg segments per utterance.
-constexpr int kMaxSegPerUtt = 32;
-__global__ void __launch_bounds__(128) cam_gate_kernel(const __nv_bfloat16* __restrict__ h,
-                                                       const int* __restrict__ utt_B, const int* __restrict__ utt_T,
-                                                       const int* __restrict__ seg_base, int seg_len,
+// CAM gate, step 1: per-segment column sums of h (bf16 [R50, 128], post BN+ReLU bottleneck).
+// One block of 128 threads per global segment g; seg_utt[g] = utterance, seg_base[u] = first segment of u.
+__global__ void __launch_bounds__(128) cam_segsum_kernel(const __nv_bfloat16* __restrict__ h,
+                                                         const int* __restrict__ utt_B, const int* __restrict__ utt_T,
+                                                         const int* __restrict__ seg_base, const int* __restrict__ seg_utt,
+                                                         int seg_len, float* __restrict__ seg_sum) {
+  const int g = blockIdx.x, c = threadIdx.x;
+  const int u = seg_utt[g];
+  const int s = g - seg_base[u];
+  const int B = utt_B[u], T = utt_T[u];
+  const int t0 = s * seg_len, t1 = min(T, t0 + seg_len);
+  float a = 0.f;
+  for (int t = t0; t < t1; ++t) a += __bfloat162float(h[(size_t)(B + t) * 128 + c]);
+  seg_sum[(size_t)g * 128 + c] = a;
+}
+
+// CAM gate, step 2: ctx = mean over the whole utterance + mean over the segment (last segment partial, like
+// avg_pool1d(ceil_mode=True)); gate[g] = sigmoid(W2 relu(W1 ctx + b1) + b2).  One block per global segment.
+__global__ void __launch_bounds__(128) cam_gate_kernel(const float* __restrict__ seg_sum,
+                                                       const int* __restrict__ utt_T, const int* __restrict__ seg_base,
+                                                       const int* __restrict__ seg_utt, int seg_len,
                                                        const float* __restrict__ w1 /* [64][128] */,
                                                        const float* __restrict__ b1,
                                                        const float* __restrict__ w2 /* [32][64] */,
                                                        const float* __restrict__ b2, float* __restrict__ gate) {
-  __shared__ float seg_sum[kMaxSegPerUtt][128];
   __shared__ float ctx[128];
   __shared__ float hid[64];
-  const int u = blockIdx.x, c = threadIdx.x;
-  const int B = utt_B[u], T = utt_T[u];
+  const int g = blockIdx.x, c = threadIdx.x;
+  const int u = seg_utt[g];
+  const int sb = seg_base[u];
+  const int s = g - sb;
+  const int T = utt_T[u];
   const int nseg = (T + seg_len - 1) / seg_len;
   float total = 0.f;
-  for (int s = 0; s < nseg; ++s) {
-    const int t1 = min(T, (s + 1) * seg_len);
+  for (int k = 0; k < nseg; ++k) total += seg_sum[(size_t)(sb + k) * 128 + c];
+  const int n = min(T, (s + 1) * seg_len) - s * seg_len;
+  ctx[c] = total / (float)T + seg_sum[(size_t)g * 128 + c] / (float)n;
+  __syncthreads();
+  {  // 64 outputs x 128 inputs: two threads per output, combined by shuffle
+    const int o = c >> 1, half = c & 1;
     float a = 0.f;
-    for (int t = s * seg_len; t < t1; ++t) a += __bfloat162float(h[(size_t)(B + t) * 128 + c]);
-    seg_sum[s][c] = a;
-    total += a;
+    for (int k = half * 64; k < half * 64 + 64; ++k) a += w1[o * 128 + k] * ctx[k];
+    a += __shfl_xor_sync(0xffffffffu, a, 1);
+    if (half == 0) hid[o] = fmaxf(a + b1[o], 0.f);
   }
-  const float gmean = total / (float)T;
-  for (int s = 0; s < nseg; ++s) {
-    const int n = min(T, (s + 1) * seg_len) - s * seg_len;
-    __syncthreads();
-    ctx[c] = gmean + seg_sum[s][c] / (float)n;
-    __syncthreads();
-    if (c < 64) {
-      float a = b1[c];
-      for (int k = 0; k < 128; ++k) a += w1[c * 128 + k] * ctx[k];
-      hid[c] = fmaxf(a, 0.f);
-    }
-    __syncthreads();
-    if (c < 32) {
-      float a = b2[c];
-      for (int k = 0; k < 64; ++k) a += w2[c * 64 + k] * hid[k];
-      gate[(size_t)(seg_base[u] + s) * 32 + c] = 1.0f / (1.0f + expf(-a));
-    }
+  __syncthreads();
+  if (c < 32) {
+    float a = b2[c];
+    for (int k = 0; k < 64; ++k) a += w2[c * 64 + k] * hid[k];
+    gate[(size_t)g * 32 + c] = 1.0f / (1.0f + expf(-a));
   }
 }
 

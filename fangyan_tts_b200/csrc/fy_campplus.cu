@@ -118,16 +118,16 @@ size_t align_up(size_t x, size_t a = 1024) { return (x + a - 1) / a * a; }
 
 struct Layout {
   int n_utts, R50, R100, n_seg;
-  size_t m_B, m_T2, m_segbase, m_rowsrc, m_rowseg, meta_ints;
+  size_t m_B, m_T2, m_segbase, m_rowsrc, m_rowseg, m_segutt, meta_ints;
   size_t o_meta, o_m42s, o_m42, o_m22s, o_m22, o_m11s, o_x0, o_y40, o_s40, o_z40a, o_z40b, o_y20, o_s20, o_z20a, o_z20b,
-      o_fcm, o_cat[4], o_hin, o_hb, o_gate, o_stats, total;
+      o_fcm, o_cat[4], o_hin, o_hb, o_gate, o_segsum, o_stats, total;
 };
 
 Layout make_layout(const CamPlan* p, int n_utts, int r50, int n_seg) {
   Layout l;
   l.n_utts = n_utts; l.R50 = r50; l.R100 = 2 * r50 + 4; l.n_seg = n_seg;
   l.m_B = 0; l.m_T2 = n_utts; l.m_segbase = 2 * (size_t)n_utts; l.m_rowsrc = 3 * (size_t)n_utts;
-  l.m_rowseg = l.m_rowsrc + l.R100; l.meta_ints = l.m_rowseg + r50;
+  l.m_rowseg = l.m_rowsrc + l.R100; l.m_segutt = l.m_rowseg + r50; l.meta_ints = l.m_segutt + n_seg;
   const size_t R = l.R100;
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes); return at; };
@@ -148,6 +148,7 @@ Layout make_layout(const CamPlan* p, int n_utts, int r50, int n_seg) {
   l.o_hin = take((size_t)r50 * 1024 * 2);
   l.o_hb = take((size_t)r50 * 128 * 2);
   l.o_gate = take((size_t)n_seg * 32 * 4);
+  l.o_segsum = take((size_t)n_seg * 128 * 4);
   l.o_stats = take((size_t)n_utts * 2 * c * 4);
   l.total = o;
   return l;
@@ -343,7 +344,6 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
     FY_CHECK(T >= 3, FY_ERR_ARG, "fy_campplus_forward: utterance %d has %d frames (need >= 3)", u, T);
     T2[u] = (T - 1) / 2 + 1;
     const int ns = (T2[u] + cf.seg_len - 1) / cf.seg_len;
-    FY_CHECK(ns <= camk::kMaxSegPerUtt, FY_ERR_ARG, "fy_campplus_forward: utterance %d too long (%d frames)", u, T);
     B[u] = row; SB[u] = nseg;
     vT += T; vT2 += T2[u];
     row += T2[u] + 2;
@@ -366,13 +366,14 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
     const int T = h_frame_off[u + 1] - h_frame_off[u];
     for (int t = 0; t < T; ++t) hm[lay.m_rowsrc + 2 * B[u] + 2 + t] = h_frame_off[u] + t;
     for (int t = 0; t < T2[u]; ++t) hm[lay.m_rowseg + B[u] + t] = SB[u] + t / cf.seg_len;
+    for (int k = 0; k * cf.seg_len < T2[u]; ++k) hm[lay.m_segutt + SB[u] + k] = u;
   }
   uint8_t* base = reinterpret_cast<uint8_t*>(ws);
   int* d_meta = reinterpret_cast<int*>(base + lay.o_meta);
   FY_CUDA(cudaMemcpyAsync(d_meta, hm, lay.meta_ints * 4, cudaMemcpyHostToDevice, st));
   FY_CUDA(cudaEventRecord(p->meta_ev, st));
   const int *d_B = d_meta + lay.m_B, *d_T2 = d_meta + lay.m_T2, *d_segbase = d_meta + lay.m_segbase;
-  const int *d_rowsrc = d_meta + lay.m_rowsrc, *d_rowseg = d_meta + lay.m_rowseg;
+  const int *d_rowsrc = d_meta + lay.m_rowsrc, *d_rowseg = d_meta + lay.m_rowseg, *d_segutt = d_meta + lay.m_segutt;
   auto I = [&](size_t off) { return reinterpret_cast<int*>(base + off); };
   auto H = [&](size_t off) { return reinterpret_cast<__nv_bfloat16*>(base + off); };
   auto Fp = [&](size_t off) { return reinterpret_cast<float*>(base + off); };
@@ -428,6 +429,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   __nv_bfloat16* hin = H(lay.o_hin);
   __nv_bfloat16* hb = H(lay.o_hb);
   float* gate = Fp(lay.o_gate);
+  float* segsum = Fp(lay.o_segsum);
   CUtensorMap m_hb;
   FY_TRY(make_tmap_bf16(&m_hb, hb, R50, 128, 128, 128));
   for (int b = 0; b < cf.n_blocks; ++b) {
@@ -449,8 +451,9 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
         g.epi.scale = d.bn2.scale; g.epi.bias = d.bn2.shift; g.epi.row_idx = d_rowseg;
         FY_TRY(run_gemm(c, g, 2.0 * vT2 * 128 * d.cin));
       }
-      c->launches += 2;  // bnrelu, cam_gate
-      camk::cam_gate_kernel<<<n_utts, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
+      c->launches += 3;  // bnrelu, cam_segsum, cam_gate
+      camk::cam_segsum_kernel<<<nseg, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, d_segutt, cf.seg_len, segsum);
+      camk::cam_gate_kernel<<<nseg, 128, 0, st>>>(segsum, d_T2, d_segbase, d_segutt, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
       {
         GemmArgs g;
         g.tmap_a = m_hb; g.tmap_b = d.ml; g.M = R50; g.N = 32;

@@ -30,7 +30,8 @@ struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+  static constexpr int kAccStages = BN == 32 ? 4 : 2;   // TMEM accumulator ring
+  static constexpr int kTmemCols = kAccStages * BN < 32 ? 32 : kAccStages * BN;
   // tiles + barriers + scale/bias staging + alignment slack
   static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 2 * BN * 4 + 1024;
 };
@@ -51,8 +52,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tfull_bar = empty_bar + C::kStages;
-  uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* tempty_bar = tfull_bar + C::kAccStages;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + C::kAccStages);
   float* s_scale = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);
   float* s_bias = s_scale + BN;
 
@@ -72,7 +73,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       ptx::mbar_init(&full_bar[i], 1);
       ptx::mbar_init(&empty_bar[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < C::kAccStages; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
       ptx::mbar_init(&tempty_bar[i], kEpiThreads);
     }
@@ -137,7 +138,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
           }
         }
         ptx::mma_commit(&tfull_bar[as]);
-        if (++as == 2) { as = 0; aphase ^= 1; }
+        if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
       }
     }
   } else if (warp >= 4) {
@@ -147,15 +148,19 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     const GemmEpi& e = args.epi;
     int as = 0;
     uint32_t aphase = 0;
+    int staged_n0 = -1;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / num_n) * BM;
       const int n0 = (tile % num_n) * BN;
-      asm volatile("bar.sync 1, 128;\n" ::: "memory");
-      for (int i = et; i < BN; i += kEpiThreads) {
-        s_scale[i] = e.scale ? __ldg(e.scale + n0 + i) : 1.0f;
-        s_bias[i] = e.bias ? __ldg(e.bias + n0 + i) : 0.0f;
+      if (n0 != staged_n0) {  // per-column scale / bias of this N block -> shared memory (uniform branch)
+        asm volatile("bar.sync 1, 128;\n" ::: "memory");
+        for (int i = et; i < BN; i += kEpiThreads) {
+          s_scale[i] = e.scale ? __ldg(e.scale + n0 + i) : 1.0f;
+          s_bias[i] = e.bias ? __ldg(e.bias + n0 + i) : 0.0f;
+        }
+        asm volatile("bar.sync 1, 128;\n" ::: "memory");
+        staged_n0 = n0;
       }
-      asm volatile("bar.sync 1, 128;\n" ::: "memory");
       const int row = m0 + q * 32 + lane;
       bool row_ok = row < args.M;
       int ridx = 0;
@@ -163,6 +168,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       if (ridx == -2) row_ok = false;  // -2: leave the output row untouched; -1: write zeros
       const bool keep = ridx >= 0;
       const size_t orow = e.remap_q ? (size_t)(row / e.remap_q) * e.remap_fp + row % e.remap_q + e.remap_add : (size_t)row;
+      uint4 rpre[4];
+      if (e.resid && row_ok) {  // first chunk of the residual: issue the loads before waiting for the accumulator
+        const uint4* rp = reinterpret_cast<const uint4*>(e.resid + orow * e.ldo + (size_t)e.col_off + n0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rpre[j] = __ldg(rp + j);
+      }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
@@ -179,7 +190,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             const uint4* rp = reinterpret_cast<const uint4*>(e.resid + orow * e.ldo + col);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const uint4 w = __ldg(rp + j);
+              const uint4 w = c == 0 ? rpre[j] : __ldg(rp + j);
               const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
@@ -252,7 +263,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(&tempty_bar[as]);
-      if (++as == 2) { as = 0; aphase ^= 1; }
+      if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
     }
   }
 

@@ -137,35 +137,48 @@ __global__ void __launch_bounds__(256) rope_split_kernel(const float* __restrict
   }
 }
 
-// FSMN memory: x[row, c] += v[row, c] + sum_j w[c][j] * v[row + j - pad, c] over rows of the same utterance.
-// v is the fp32 value projection inside qkv (column offset 2D).  One thread per (row, 4 channels).
+// FSMN memory: x[row, c] += v[row, c] + sum_j w[j][c] * v[row + j - pad, c] over rows of the same utterance.
+// v is the fp32 value projection inside qkv (column offset 2D).  A block stages a (64 + KS - 1) x 64 tile of v in
+// shared memory so every value is fetched from L2 once instead of KS times.  grid: (ceil(rows / 64), D / 64).
+constexpr int kFsmnRows = 64, kFsmnCols = 64, kFsmnMaxK = 31;
 __global__ void __launch_bounds__(256) fsmn_kernel(const float* __restrict__ qkv, const int* __restrict__ row_utt,
-                                                   const int* __restrict__ row_pos, const int* __restrict__ utt_L,
                                                    const float* __restrict__ w /* [KS][D] tap-major */, int rows, int D,
                                                    int KS, float* __restrict__ x) {
-  const int per_row = D / 4;
-  const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (idx >= (size_t)rows * per_row) return;
-  const int row = (int)(idx / per_row);
-  const int c = (int)(idx % per_row) * 4;
-  const int u = __ldg(row_utt + row);
-  if (u < 0) return;
-  const int pos = __ldg(row_pos + row);
-  const int L = __ldg(utt_L + u);
+  __shared__ float4 sv[kFsmnRows + kFsmnMaxK - 1][kFsmnCols / 4];
+  __shared__ float4 sw[kFsmnMaxK][kFsmnCols / 4];
+  __shared__ int sutt[kFsmnRows + kFsmnMaxK - 1];
   const int pad = (KS - 1) / 2;
+  const int r0 = blockIdx.x * kFsmnRows, c0 = blockIdx.y * kFsmnCols;
+  const int span = kFsmnRows + KS - 1;
   const size_t ldv = (size_t)3 * D;
-  const float* vbase = qkv + 2 * D + c;
-  float4 acc = *reinterpret_cast<const float4*>(vbase + (size_t)row * ldv);
-  const int j0 = max(0, pad - pos), j1 = min(KS, L - pos + pad);
-  for (int j = j0; j < j1; ++j) {
-    const float4 vv = *reinterpret_cast<const float4*>(vbase + (size_t)(row + j - pad) * ldv);
-    const float4 ww = __ldg(reinterpret_cast<const float4*>(w + (size_t)j * D + c));
-    acc.x += ww.x * vv.x; acc.y += ww.y * vv.y; acc.z += ww.z * vv.z; acc.w += ww.w * vv.w;
+  for (int i = threadIdx.x; i < span * 16; i += 256) {
+    const int rr = i >> 4, c4 = i & 15;
+    const int row = r0 - pad + rr;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row >= 0 && row < rows) v = *reinterpret_cast<const float4*>(qkv + (size_t)row * ldv + 2 * D + c0 + c4 * 4);
+    sv[rr][c4] = v;
+    if (c4 == 0) sutt[rr] = (row >= 0 && row < rows) ? __ldg(row_utt + row) : -1;
   }
-  float4* xp = reinterpret_cast<float4*>(x + (size_t)row * D + c);
-  float4 xv = *xp;
-  xv.x += acc.x; xv.y += acc.y; xv.z += acc.z; xv.w += acc.w;
-  *xp = xv;
+  for (int i = threadIdx.x; i < KS * 16; i += 256)
+    sw[i >> 4][i & 15] = __ldg(reinterpret_cast<const float4*>(w + (size_t)(i >> 4) * D + c0 + (i & 15) * 4));
+  __syncthreads();
+  for (int it = threadIdx.x; it < kFsmnRows * 16; it += 256) {
+    const int t = it >> 4, c4 = it & 15;
+    const int row = r0 + t;
+    const int u = sutt[t + pad];
+    if (row >= rows || u < 0) continue;
+    float4 acc = sv[t + pad][c4];
+    for (int j = 0; j < KS; ++j) {
+      if (sutt[t + j] == u) {
+        const float4 vv = sv[t + j][c4], ww = sw[j][c4];
+        acc.x += ww.x * vv.x; acc.y += ww.y * vv.y; acc.z += ww.z * vv.z; acc.w += ww.w * vv.w;
+      }
+    }
+    float4* xp = reinterpret_cast<float4*>(x + (size_t)row * D + c0 + c4 * 4);
+    float4 xv = *xp;
+    xv.x += acc.x; xv.y += acc.y; xv.z += acc.z; xv.w += acc.w;
+    *xp = xv;
+  }
 }
 
 // FSQ: z = W[8, D] x + b -> tanh -> * scale -> pre; id = sum (rint(pre) + 1) * 3^i.  One warp per token row;
