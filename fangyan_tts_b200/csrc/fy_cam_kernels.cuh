@@ -102,9 +102,9 @@ __global__ void __launch_bounds__(128) cam_segsum_kernel(const __nv_bfloat16* __
 __global__ void __launch_bounds__(128) cam_gate_kernel(const float* __restrict__ seg_sum,
                                                        const int* __restrict__ utt_T, const int* __restrict__ seg_base,
                                                        const int* __restrict__ seg_utt, int seg_len,
-                                                       const float* __restrict__ w1 /* [64][128] */,
+                                                       const float* __restrict__ w1 /* [128][64] (in, out) */,
                                                        const float* __restrict__ b1,
-                                                       const float* __restrict__ w2 /* [32][64] */,
+                                                       const float* __restrict__ w2 /* [64][32] (in, out) */,
                                                        const float* __restrict__ b2, float* __restrict__ gate) {
   __shared__ float ctx[128];
   __shared__ float hid[64];
@@ -122,14 +122,14 @@ __global__ void __launch_bounds__(128) cam_gate_kernel(const float* __restrict__
   {  // 64 outputs x 128 inputs: two threads per output, combined by shuffle
     const int o = c >> 1, half = c & 1;
     float a = 0.f;
-    for (int k = half * 64; k < half * 64 + 64; ++k) a += w1[o * 128 + k] * ctx[k];
+    for (int k = half * 64; k < half * 64 + 64; ++k) a += w1[k * 64 + o] * ctx[k];
     a += __shfl_xor_sync(0xffffffffu, a, 1);
     if (half == 0) hid[o] = fmaxf(a + b1[o], 0.f);
   }
   __syncthreads();
   if (c < 32) {
     float a = b2[c];
-    for (int k = 0; k < 64; ++k) a += w2[c * 64 + k] * hid[k];
+    for (int k = 0; k < 64; ++k) a += w2[k * 32 + c] * hid[k];
     gate[(size_t)g * 32 + c] = 1.0f / (1.0f + expf(-a));
   }
 }

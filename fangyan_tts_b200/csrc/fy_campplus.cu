@@ -238,9 +238,12 @@ int fy_load_campplus(fy_ctx* ctx, const fy_tensor* t, int n, const fy_campplus_c
       FY_TRY(make_tmap_bf16(&d.ml, d.wl, 32, 384, 384, 32));
       GET(a1, pre + ".cam.lin1.weight", 64 * 128); GET(a1b, pre + ".cam.lin1.bias", 64);
       GET(a2, pre + ".cam.lin2.weight", 32 * 64); GET(a2b, pre + ".cam.lin2.bias", 32);
-      FY_TRY(dev_upload(p, std::vector<float>(a1->h_data, a1->h_data + 64 * 128), &d.cw1));
+      std::vector<float> t1((size_t)128 * 64), t2((size_t)64 * 32);  // transposed to (in, out) for coalesced reads
+      for (int o = 0; o < 64; ++o) for (int k = 0; k < 128; ++k) t1[(size_t)k * 64 + o] = a1->h_data[o * 128 + k];
+      for (int o = 0; o < 32; ++o) for (int k = 0; k < 64; ++k) t2[(size_t)k * 32 + o] = a2->h_data[o * 64 + k];
+      FY_TRY(dev_upload(p, t1, &d.cw1));
       FY_TRY(dev_upload(p, std::vector<float>(a1b->h_data, a1b->h_data + 64), &d.cb1));
-      FY_TRY(dev_upload(p, std::vector<float>(a2->h_data, a2->h_data + 32 * 64), &d.cw2));
+      FY_TRY(dev_upload(p, t2, &d.cw2));
       FY_TRY(dev_upload(p, std::vector<float>(a2b->h_data, a2b->h_data + 32), &d.cb2));
     }
     ch += cfg->layers[b] * cfg->growth;

@@ -178,8 +178,8 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
   FY_CHECK(cfg->d_model / cfg->n_head == 64, FY_ERR_ARG, "fy_load_s3tok: head_dim must be 64 (got %d)",
            cfg->d_model / cfg->n_head);
   FY_CHECK(cfg->fsq_dim == 8, FY_ERR_ARG, "fy_load_s3tok: fsq_dim must be 8");
-  FY_CHECK(cfg->fsmn_kernel >= 1 && cfg->fsmn_kernel <= s3k::kFsmnMaxK && cfg->fsmn_kernel % 2 == 1 && cfg->d_model % 64 == 0, FY_ERR_ARG,
-           "fy_load_s3tok: fsmn_kernel must be odd and <= %d", s3k::kFsmnMaxK);
+  FY_CHECK(cfg->fsmn_kernel == s3k::kFsmnMaxK && cfg->d_model % 64 == 0, FY_ERR_ARG,
+           "fy_load_s3tok: the FSMN kernel is instantiated for fsmn_kernel == %d only", s3k::kFsmnMaxK);
   s3_free_plan(c);
   S3Plan* p = new S3Plan();
   c->s3_plan = p;
@@ -438,7 +438,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
     }
     {
       dim3 fg((Rtok + s3k::kFsmnRows - 1) / s3k::kFsmnRows, D / s3k::kFsmnCols);
-      s3k::fsmn_kernel<<<fg, 256, 0, st>>>(b_qkv, d_rutt, Lw.fsmn, Rtok, D, cf.fsmn_kernel, b_x);
+      s3k::fsmn_kernel<31><<<fg, 128, 0, st>>>(b_qkv, d_rutt, Lw.fsmn, Rtok, D, b_x);
     }
     {
       const int pi = prof_begin(c, PK_ATTN);
