@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--utts", type=int, default=int(os.environ.get("FY_BENCH_UTTS", "1000")))
     ap.add_argument("--precision", default=os.environ.get("FY_PRECISION", "bf16x3"), choices=["bf16", "bf16x3"])
     ap.add_argument("--batch-seconds", type=float, default=float(os.environ.get("FY_BATCH_SECONDS", "2400")))
-    ap.add_argument("--cpu-sample", type=int, default=6, help="utterances in the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=96, help="utterances in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -108,23 +108,36 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------ CPU arm
 
 
+_CPU_MODELS = []
+
+
 def cpu_reference_rate(utts, threads: int):
-    """The reference's per-utterance path restated on the CPU (oracle/; torch fp32, batch 1, true length):
-    returns (audio-hours/s, audio seconds processed, wall seconds)."""
+    """The reference's per-utterance path restated on the CPU (oracle/; torch fp32, batch 1, true length), driven the
+    way the reference drives it: a ThreadPoolExecutor with one utterance per worker thread and intra-op parallelism 1
+    (extract_embedding.py:81-82,100).  Returns (audio-hours/s, audio seconds processed, wall seconds)."""
     import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from fangyan_tts_b200 import synth_weights
     from oracle import campplus as CP, frontend as F, s3tokenizer as S3
-    torch.set_num_threads(threads)
-    cam = CP.init_random(CP.CamPlus())
-    s3 = S3.init_random(S3.S3Tokenizer())
-    t0 = time.perf_counter()
-    secs = 0.0
-    for u in utts:
+    torch.set_num_threads(1)
+    if not _CPU_MODELS:
+        cam, s3 = CP.CamPlus(), S3.S3Tokenizer()                 # same random-init tensors as the GPU arm
+        cam.load_state_dict({k: torch.from_numpy(v) for k, v in synth_weights.campplus_state().items()}, strict=False)
+        s3.load_state_dict({k: torch.from_numpy(v) for k, v in synth_weights.s3tok_state().items()})
+        _CPU_MODELS.extend([cam.eval(), s3.eval()])
+    cam, s3 = _CPU_MODELS
+
+    def single_job(u):
         x = torch.from_numpy(u.astype(np.float32) / 32768.0)[None]
         CP.embed_one(cam, F.cmn(F.kaldi_fbank(x)))
         if F.stage2_gate(x.shape[1]):
             S3.tokenize_one(s3, F.whisper_log_mel(x))
-        secs += len(u) / 16000.0
-    wall = time.perf_counter() - t0
+        return len(u) / 16000.0
+
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        t0 = time.perf_counter()
+        secs = sum(ex.map(single_job, utts))
+        wall = time.perf_counter() - t0
     return secs / 3600.0 / wall, secs, wall
 
 
@@ -136,7 +149,8 @@ def run_ours(args):
     import torch.distributed as dist
     from fangyan_tts_b200.engine import Engine
     from fangyan_tts_b200.pipeline import Extractor, Utt, plan_batches
-    from oracle import campplus as CP, s3tokenizer as S3  # weights only: random-init state dicts of the named nets
+    from fangyan_tts_b200 import synth_weights
+    from fangyan_tts_b200.configs import CamPlusConfig, S3Config
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -145,13 +159,9 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = Engine(local, args.precision)
-    cam_cfg, s3_cfg = CP.CamPlusConfig(), S3.S3Config()
-    eng.load_campplus(dict(CP.init_random(CP.CamPlus(cam_cfg)).state_dict()), cam_cfg)
-    s3 = S3.init_random(S3.S3Tokenizer(s3_cfg))
-    st = dict(s3.state_dict())
-    st["rope.cos"], st["rope.sin"] = S3.rope_tables(2048, s3_cfg.d_head, s3_cfg.rope_theta)
-    eng.load_s3tok(st, s3_cfg)
-    del s3, st
+    cam_cfg, s3_cfg = CamPlusConfig(), S3Config()
+    eng.load_campplus(synth_weights.campplus_state(cam_cfg), cam_cfg)   # random-init weights of the named architectures
+    eng.load_s3tok(synth_weights.s3tok_state(s3_cfg), s3_cfg)
 
     utts = workload(args.utts, 1986 + 2 + rank)          # weak scaling: every rank owns its own shard
     audio_s = sum(len(u) for u in utts) / 16000.0

@@ -1,0 +1,238 @@
+"""Drop-in command lines for stages 1-2 (contract B1).
+
+Same flags, inputs and outputs as the reference's tools/extract_embedding.py:61-102 and
+tools/extract_speech_token.py:61-96:
+
+    extract_embedding.py    --dir D --onnx_path campplus.onnx            [--num_thread 8]
+        reads D/wav.scp, D/utt2spk         writes D/utt2embedding.pt, D/spk2embedding.pt
+    extract_speech_token.py --dir D --onnx_path speech_tokenizer_v3.onnx [--num_thread 8]
+        reads D/wav.scp                    writes D/utt2speech_token.pt
+
+What differs is inside: utterances are sorted by length, packed into batches and run through the sm_100a kernels;
+with more than one visible GPU the script spawns one worker per GPU (or joins an existing torchrun launch), shards
+the utterances by duration and gathers the results over NCCL so run.sh needs no edit.  `--num_thread` sizes the
+WAV-reader pool (the reference uses it for its per-utterance worker threads).  There is no CPU fallback: without a
+GPU or the built library the command exits non-zero and writes nothing, as the reference does on any worker error
+(extract_embedding.py:49).
+
+Environment knobs (all optional): FY_GPUS (number of GPUs, default all visible), FY_PRECISION (bf16x3 | bf16),
+FY_BATCH_SECONDS, FY_BATCH_UTTS, FY_CAMPPLUS_CONFIG / FY_S3TOK_CONFIG (JSON hyper-parameter overrides).
+"""
+from __future__ import annotations
+
+import argparse
+import collections
+import itertools
+import json
+import logging
+import math
+import os
+import sys
+import time
+from concurrent.futures import ThreadPoolExecutor
+from typing import List, Sequence
+
+import numpy as np
+
+from . import kaldi_io
+
+SR = 16000
+log = logging.getLogger("fangyan_b200")
+
+
+def parse_args(argv, prog):
+    ap = argparse.ArgumentParser(prog=prog)
+    ap.add_argument("--dir", type=str, required=True)
+    ap.add_argument("--onnx_path", type=str, required=True)
+    ap.add_argument("--num_thread", type=int, default=8)
+    return ap.parse_args(argv)
+
+
+def scan_durations(keys: Sequence[str], paths: Sequence[str], pool: ThreadPoolExecutor):
+    """Header-only pass: (frames, channels, sample_rate) per utterance, so batches can be planned before decoding."""
+    return list(pool.map(lambda kp: kaldi_io.wav_header(kp[1], kp[0]), zip(keys, paths)))
+
+
+def len16k(frames: int, sr: int) -> int:
+    """Length after torchaudio Resample(sr -> 16000): ceil(16000 * n / sr) (functional.py:1432)."""
+    if sr == SR:
+        return frames
+    g = math.gcd(sr, SR)
+    return int(math.ceil((SR // g) * frames / (sr // g)))
+
+
+def prefetch(batches, load_one, pool: ThreadPoolExecutor, depth: int = 2):
+    """Yield (batch indices, decoded utterances) while the reader pool already works on the next `depth` batches."""
+    it = iter(batches)
+    pending = collections.deque()
+    for b in itertools.islice(it, depth):
+        pending.append((b, [pool.submit(load_one, i) for i in b]))
+    while pending:
+        b, futs = pending.popleft()
+        nxt = next(it, None)
+        if nxt is not None:
+            pending.append((nxt, [pool.submit(load_one, i) for i in nxt]))
+        yield b, [f.result() for f in futs]   # a decode error propagates here with the utterance key in its message
+
+
+def _dist_env():
+    """(rank, world, local_rank) when launched under torchrun, else None."""
+    if "RANK" in os.environ and "WORLD_SIZE" in os.environ:
+        return int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
+    return None
+
+
+def _n_gpus() -> int:
+    import torch
+    if not torch.cuda.is_available():
+        from ._lib import FyError
+        raise FyError("no CUDA device visible: fangyan_b200 has no CPU path (the reference's onnxruntime CPU fallback "
+                      "is deliberately not reproduced)")
+    n = torch.cuda.device_count()
+    want = int(os.environ.get("FY_GPUS", n))
+    return max(1, min(n, want))
+
+
+def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: bool):
+    import torch
+    from . import distributed as D
+    from .audio_io import read_wav
+    from .configs import campplus_config, s3_config
+    from .engine import Engine, kaldi_num_frames
+    from .pipeline import Extractor, Utt, plan_batches, shard_indices
+    from .weights import load_state
+
+    env = _dist_env()
+    rank = env[0] if env and not spawned else local_rank
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", str(port))
+        torch.cuda.set_device(local_rank)
+        D.init(rank, world, "nccl", port, torch.device("cuda", local_rank))
+    t_start = time.perf_counter()
+    eng = Engine(local_rank, os.environ.get("FY_PRECISION", "bf16x3"))
+    state = {k: torch.from_numpy(np.ascontiguousarray(v, dtype=np.float32)) for k, v in load_state(args.onnx_path).items()
+             if v.dtype.kind == "f"}
+    if stage == 1:
+        eng.load_campplus(state, campplus_config())
+    else:
+        eng.load_s3tok(state, s3_config())
+    del state
+
+    utt2wav = kaldi_io.read_table(os.path.join(args.dir, "wav.scp"))
+    keys, paths = list(utt2wav.keys()), list(utt2wav.values())
+    pool = ThreadPoolExecutor(max_workers=max(1, args.num_thread))
+    heads = scan_durations(keys, paths, pool)
+    n16 = [len16k(fr, sr) for fr, _, sr in heads]
+    dur = [n / SR for n in n16]
+    mine = shard_indices(dur, rank, world)
+    ex = Extractor(eng, float(os.environ.get("FY_BATCH_SECONDS", "2400")), int(os.environ.get("FY_BATCH_UTTS", "4096")))
+    dev = eng.device
+
+    def load_one(i):
+        x, sr = read_wav(paths[i], keys[i])
+        return Utt(x, sr)
+
+    if stage == 1:
+        utt2spk = kaldi_io.read_table(os.path.join(args.dir, "utt2spk"))
+        missing = [k for k in keys if k not in utt2spk]
+        if missing:
+            raise KeyError(f"utt2spk lacks {len(missing)} utterances of wav.scp, e.g. {missing[:3]}")
+        spk_names = list(dict.fromkeys(utt2spk[k] for k in keys))
+        spk_index = {s: j for j, s in enumerate(spk_names)}
+        for i in mine:
+            if kaldi_num_frames(n16[i]) < 3:
+                raise ValueError(f"utterance {keys[i]}: {n16[i]} samples at 16 kHz is too short for a speaker embedding")
+        local_dur = [dur[i] for i in mine]
+        batches = [[mine[j] for j in b] for b in plan_batches(local_dur, ex.max_batch_seconds, ex.max_batch_utts)]
+        ssum = torch.zeros(len(spk_names), 192, device=dev)
+        scnt = torch.zeros(len(spk_names), dtype=torch.int32, device=dev)
+        idx_parts, emb_parts = [], []
+        for b, utts in _progress(prefetch(batches, load_one, pool), len(batches), rank, "stage 1"):
+            emb = ex.embed_batch(utts)
+            spk = torch.tensor([spk_index[utt2spk[keys[i]]] for i in b], dtype=torch.int32, device=dev)
+            eng.speaker_sum(emb, spk, len(spk_names), ssum, scnt)
+            idx_parts.append(torch.tensor(b, dtype=torch.int64, device=dev))
+            emb_parts.append(emb)
+        index = torch.cat(idx_parts) if idx_parts else torch.zeros(0, dtype=torch.int64, device=dev)
+        emb = torch.cat(emb_parts) if emb_parts else torch.zeros(0, 192, device=dev)
+        full = D.gather_stage1(index, emb, len(keys))
+        D.reduce_speakers(ssum, scnt)
+        mean = eng.speaker_mean(ssum, scnt)
+        if rank == 0:
+            kaldi_io.save_atomic(kaldi_io.embeddings_to_dict(keys, full.cpu().numpy()),
+                                 os.path.join(args.dir, "utt2embedding.pt"))
+            kaldi_io.save_atomic(kaldi_io.speaker_dict(spk_names, mean.cpu().numpy()),
+                                 os.path.join(args.dir, "spk2embedding.pt"))
+    else:
+        gated = [i for i in mine if n16[i] / SR > 30]          # extract_speech_token.py:34-36: key kept, value []
+        for i in gated:
+            logging.warning("do not support extract speech token for audio longer than 30s (%s)", keys[i])
+        todo = [i for i in mine if not n16[i] / SR > 30 and n16[i] >= 160]
+        local_dur = [dur[i] for i in todo]
+        batches = [[todo[j] for j in b] for b in plan_batches(local_dur, ex.max_batch_seconds, ex.max_batch_utts)]
+        idx_parts, cnt_parts, tok_parts = [], [], []
+        for b, utts in _progress(prefetch(batches, load_one, pool), len(batches), rank, "stage 2"):
+            tok, counts = ex.tokenize_batch(utts)
+            idx_parts.append(torch.tensor(b, dtype=torch.int64, device=dev))
+            cnt_parts.append(torch.tensor(counts, dtype=torch.int64, device=dev))
+            tok_parts.append(tok)
+        z = torch.zeros(0, dtype=torch.int64, device=dev)
+        index = torch.cat(idx_parts) if idx_parts else z
+        counts = torch.cat(cnt_parts) if cnt_parts else z
+        toks = torch.cat(tok_parts) if tok_parts else torch.zeros(0, dtype=torch.int32, device=dev)
+        _, per_utt = D.gather_stage2(index, counts, toks, len(keys))
+        if rank == 0:
+            out = {k: ([] if p is None else p.cpu().tolist()) for k, p in zip(keys, per_utt)}
+            kaldi_io.save_atomic(out, os.path.join(args.dir, "utt2speech_token.pt"))
+    torch.cuda.synchronize()
+    if rank == 0:
+        wall = time.perf_counter() - t_start
+        sys.stderr.write(json.dumps({"stage": stage, "utts": len(keys), "audio_hours": sum(dur) / 3600.0, "gpus": world,
+                                     "wall_s": wall, "precision": eng.precision}) + "\n")
+    pool.shutdown()
+    eng.close()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _progress(it, total, rank, desc):
+    if rank != 0:
+        return it
+    try:
+        from tqdm import tqdm
+        return tqdm(it, total=total, desc=desc, unit="batch")
+    except ImportError:
+        return it
+
+
+def run_stage(stage: int, argv=None, prog: str = "extract") -> int:
+    args = parse_args(argv, prog)
+    logging.basicConfig(level=logging.INFO, format="%(asctime)s %(levelname)s %(message)s")
+    for name in ("wav.scp",) + (("utt2spk",) if stage == 1 else ()):
+        if not os.path.exists(os.path.join(args.dir, name)):
+            raise FileNotFoundError(os.path.join(args.dir, name))
+    from . import _lib
+    _lib.load()                     # fail before any work when the CUDA library is not built
+    env = _dist_env()
+    if env is not None:             # already under torchrun: one rank per process
+        _worker(env[2], env[1], stage, args, int(os.environ.get("MASTER_PORT", "29531")), False)
+        return 0
+    world = _n_gpus()
+    if world == 1:
+        _worker(0, 1, stage, args, 0, True)
+        return 0
+    import torch.multiprocessing as mp
+    port = 29500 + os.getpid() % 2000
+    mp.spawn(_worker, args=(world, stage, args, port, True), nprocs=world, join=True)
+    return 0
+
+
+def main_embedding(argv=None) -> int:
+    return run_stage(1, argv, "extract_embedding.py")
+
+
+def main_speech_token(argv=None) -> int:
+    return run_stage(2, argv, "extract_speech_token.py")

@@ -545,7 +545,8 @@ int fy_resample(fy_ctx* ctx, const float* in, const int32_t* in_off, float* out,
            "fy_resample: bad arguments (n_utts=%d, %d -> %d)", n_utts, orig_freq, new_freq);
   Ctx* c = reinterpret_cast<Ctx*>(ctx);
   // torchaudio _get_sinc_resample_kernel (functional.py:1305-1402): hann-windowed sinc, width 6, rolloff 0.99,
-  // built in float64 and rounded to fp32.  Cached per (orig, new).
+  // built in float64 and rounded to fp32 -- except the phase offset -p/new, which torchaudio computes as a float32
+  // division (its arange there is int64), a quirk reproduced below.  Cached per (orig, new).
   int a = orig_freq, b = new_freq;
   while (b) { int t = a % b; a = b; b = t; }
   const int orig = orig_freq / a, newf = new_freq / a;
@@ -561,7 +562,8 @@ int fy_resample(fy_ctx* ctx, const float* in, const int32_t* in_off, float* out,
     std::vector<float> h((size_t)newf * K);
     for (int p = 0; p < newf; ++p)
       for (int k = 0; k < K; ++k) {
-        double t = ((double)(-p) / newf + (double)(k - width) / orig) * base;
+        const float phase = (float)(-p) / (float)newf;
+        double t = ((double)phase + (double)(k - width) / orig) * base;
         if (t < -lpw) t = -lpw;
         if (t > lpw) t = lpw;
         const double cw = cos(t * M_PI / lpw / 2);

@@ -61,7 +61,8 @@ def gather_stage2(index: torch.Tensor, counts: torch.Tensor, tokens: torch.Tenso
     < 6561 so they travel as int16).  Returns (counts [n_total], list of per-utterance int tensors)."""
     idx = torch.cat(all_gather_rows(index))
     cnt = torch.cat(all_gather_rows(counts))
-    tok = torch.cat(all_gather_rows(tokens.to(torch.int16))).to(torch.int32)
+    wire = tokens.to(torch.int16).contiguous().view(torch.uint8).view(-1, 2)   # bytes: every backend moves uint8
+    tok = torch.cat(all_gather_rows(wire)).contiguous().view(torch.int16).view(-1).to(torch.int32)
     pieces = torch.split(tok, cnt.tolist())
     out: List[torch.Tensor] = [None] * n_total  # type: ignore
     full = torch.zeros(n_total, dtype=counts.dtype, device=counts.device)

@@ -99,7 +99,12 @@ class Engine:
         keep = []
         arr = (FyTensor * len(state))()
         for i, (name, t) in enumerate(state.items()):
-            a = np.ascontiguousarray(t.detach().cpu().to(torch.float32).numpy())
+            if isinstance(t, np.ndarray):
+                if t.dtype.kind != "f":
+                    t = np.zeros(0, np.float32) if t.dtype.kind in "iu" and t.ndim == 0 else t.astype(np.float32)
+                a = np.ascontiguousarray(t, dtype=np.float32)
+            else:
+                a = np.ascontiguousarray(t.detach().cpu().to(torch.float32).numpy())
             keep.append(a)
             if a.ndim > 4:
                 raise ValueError(f"{name}: rank {a.ndim} > 4")

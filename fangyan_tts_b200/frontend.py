@@ -1,0 +1,58 @@
+"""Online twin of stages 1-2 (contract B2): the two CosyVoiceFrontEnd methods, backed by the sm_100a kernels.
+
+Mirrors cosyvoice/cli/frontend.py:95-118 of the reference (method names, argument meaning, return types, asserts):
+    _extract_speech_token(prompt_wav)  -> (int32 [1, L], int32 [1]) on the device; asserts the clip is <= 30 s
+    _extract_spk_embedding(prompt_wav) -> float32 [1, 192] on the device
+and its loader cosyvoice/utils/file_utils.py:44-50 (channel MEAN first, then resample; sample rate must be >= 16 kHz)
+-- note this differs from the stage CLIs, which take channel 0 for stage 1.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .audio_io import read_wav
+from .configs import campplus_config, s3_config
+from .engine import Engine
+from .weights import load_state
+
+SR = 16000
+
+
+class CosyVoiceFrontEndB200:
+    """Construct with the same two model paths CosyVoiceFrontEnd takes (frontend.py:32-48)."""
+
+    def __init__(self, campplus_model: str, speech_tokenizer_model: str, device: int = 0, precision: str = "bf16x3"):
+        self.engine = Engine(device, precision)
+        self.device = self.engine.device
+
+        def tensors(path):
+            return {k: torch.from_numpy(np.ascontiguousarray(v, dtype=np.float32)) for k, v in load_state(path).items()
+                    if v.dtype.kind == "f"}
+
+        self.engine.load_campplus(tensors(campplus_model), campplus_config())
+        self.engine.load_s3tok(tensors(speech_tokenizer_model), s3_config())
+
+    def load_wav(self, wav, target_sr: int = SR, min_sr: int = SR) -> torch.Tensor:
+        """file_utils.load_wav: float32 [N] mono at 16 kHz on the device."""
+        x, sr = read_wav(wav, str(wav))
+        x = x.astype(np.float32) / 32768.0 if x.dtype == np.int16 else x.astype(np.float32)
+        mono = torch.from_numpy(np.ascontiguousarray(x.mean(axis=1, dtype=np.float32))).to(self.device)
+        if sr != target_sr:
+            assert sr >= min_sr, 'wav sample rate {} must be greater than {}'.format(sr, target_sr)
+            mono, _ = self.engine.resample(mono, [mono.numel()], sr, target_sr)
+        return mono
+
+    def _extract_speech_token(self, prompt_wav):
+        speech = self.load_wav(prompt_wav, SR)
+        assert speech.numel() / SR <= 30, 'do not support extract speech token for audio longer than 30s'
+        mel, frames = self.engine.logmel(speech, [speech.numel()])
+        tok, counts = self.engine.s3tok(mel, frames)
+        speech_token = tok.view(1, -1).to(torch.int32)
+        speech_token_len = torch.tensor([speech_token.shape[1]], dtype=torch.int32, device=self.device)
+        return speech_token, speech_token_len
+
+    def _extract_spk_embedding(self, prompt_wav):
+        speech = self.load_wav(prompt_wav, SR)
+        feat, frames = self.engine.fbank_cmn(speech, [speech.numel()])
+        return self.engine.campplus(feat, frames).view(1, -1)

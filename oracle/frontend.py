@@ -60,7 +60,10 @@ def resample_kernel(orig_freq: int, new_freq: int, lowpass_filter_width: int = 6
     base = min(orig, new) * rolloff
     width = math.ceil(lowpass_filter_width * orig / base)
     idx = np.arange(-width, width + orig, dtype=np.float64)[None, :] / orig
-    t = np.arange(0, -new, -1, dtype=np.float64)[:, None] / new + idx
+    # torchaudio builds the phase offsets from an int64 arange, so `/ new` is a float32 division (its `dtype`
+    # argument is None at this call); only `idx` is float64.  Reproduced here or 22.05/44.1 kHz differ by ~7e-6.
+    phase = (np.arange(0, -new, -1).astype(np.float32) / np.float32(new)).astype(np.float64)
+    t = phase[:, None] + idx
     t = t * base
     t = np.clip(t, -lowpass_filter_width, lowpass_filter_width)
     window = np.cos(t * math.pi / lowpass_filter_width / 2) ** 2
