@@ -3,6 +3,7 @@
 // statistics pooling and the final dense layer.  Convolutions with >= 32 input channels run on the tcgen05 GEMM.
 #pragma once
 #include "fy_common.cuh"
+#include "fy_ptx.cuh"
 
 namespace fy {
 namespace camk {
@@ -13,13 +14,14 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 }
 
 // Stem: Conv2d(1, 32, 3x3, pad 1) + BN + ReLU over (freq, time).  feat is packed [frames, 80] fp32.
-// out: [R100, 82, 32] bf16 channels-last with zero columns at p = 0 and p = 81 (buffer pre-zeroed).
+// out: [R100, 82, 32] fp32 (rounded to tf32: it is the A operand of the first FCM GEMM) channels-last with zero
+// columns at p = 0 and p = 81 (buffer pre-zeroed).
 // rowsrc[r] = feat row of time row r or -1 for guard rows.  w: [32][3 (freq)][3 (time)].
 // grid = R100, block = 320 (80 freq x 4 groups of 8 channels).
 __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ feat, const int* __restrict__ rowsrc,
                                                    int R100, const float* __restrict__ w,
                                                    const float* __restrict__ scale, const float* __restrict__ shift,
-                                                   __nv_bfloat16* __restrict__ out) {
+                                                   float* __restrict__ out) {
   const int r = blockIdx.x;
   const int src = rowsrc[r];
   if (src < 0) return;
@@ -49,11 +51,11 @@ __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ fea
     for (int i = 0; i < 3; ++i)
 #pragma unroll
       for (int j = 0; j < 3; ++j) a += sw[c * 9 + i * 3 + j] * x[i][j];
-    y[k] = fmaxf(a * sw[288 + c] + sw[320 + c], 0.f);
+    y[k] = ptx::round_tf32(fmaxf(a * sw[288 + c] + sw[320 + c], 0.f));
   }
-  uint4 o;
-  o.x = pack2(y[0], y[1]); o.y = pack2(y[2], y[3]); o.z = pack2(y[4], y[5]); o.w = pack2(y[6], y[7]);
-  *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8) = o;
+  float4* dst = reinterpret_cast<float4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8);
+  dst[0] = make_float4(y[0], y[1], y[2], y[3]);
+  dst[1] = make_float4(y[4], y[5], y[6], y[7]);
 }
 
 // mask[g] = -2 (skip) when slot g % Q is outside [lo, hi]; else -1 (write zero) on guard time rows; else 0
@@ -64,10 +66,10 @@ __global__ void pos_mask_kernel(const int* __restrict__ rowsrc, int R, int Q, in
   mask[g] = (p < lo || p > hi) ? -2 : (rowsrc[g / Q] >= 0 ? 0 : -1);
 }
 
-// y = bf16(relu(x * scale[c] + shift[c])) for c < C; x fp32 [R, ldx], y bf16 [R, ldy].  4 channels per thread.
+// y = tf32(relu(x * scale[c] + shift[c])) for c < C; x fp32 [R, ldx], y fp32 [R, ldy].  4 channels per thread.
 __global__ void __launch_bounds__(256) bnrelu_kernel(const float* __restrict__ x, int ldx, int R, int C,
                                                      const float* __restrict__ scale, const float* __restrict__ shift,
-                                                     __nv_bfloat16* __restrict__ y, int ldy) {
+                                                     float* __restrict__ y, int ldy) {
   const int per_row = C / 4;
   const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
   if (idx >= (size_t)R * per_row) return;
@@ -75,15 +77,17 @@ __global__ void __launch_bounds__(256) bnrelu_kernel(const float* __restrict__ x
   const float4 v = *reinterpret_cast<const float4*>(x + (size_t)r * ldx + c);
   const float4 s = __ldg(reinterpret_cast<const float4*>(scale + c));
   const float4 b = __ldg(reinterpret_cast<const float4*>(shift + c));
-  uint2 o;
-  o.x = pack2(fmaxf(v.x * s.x + b.x, 0.f), fmaxf(v.y * s.y + b.y, 0.f));
-  o.y = pack2(fmaxf(v.z * s.z + b.z, 0.f), fmaxf(v.w * s.w + b.w, 0.f));
-  *reinterpret_cast<uint2*>(y + (size_t)r * ldy + c) = o;
+  float4 o;
+  o.x = ptx::round_tf32(fmaxf(v.x * s.x + b.x, 0.f));
+  o.y = ptx::round_tf32(fmaxf(v.y * s.y + b.y, 0.f));
+  o.z = ptx::round_tf32(fmaxf(v.z * s.z + b.z, 0.f));
+  o.w = ptx::round_tf32(fmaxf(v.w * s.w + b.w, 0.f));
+  *reinterpret_cast<float4*>(y + (size_t)r * ldy + c) = o;
 }
 
-// CAM gate, step 1: per-segment column sums of h (bf16 [R50, 128], post BN+ReLU bottleneck).
+// CAM gate, step 1: per-segment column sums of h (fp32 [R50, 128], post BN+ReLU bottleneck).
 // One block of 128 threads per global segment g; seg_utt[g] = utterance, seg_base[u] = first segment of u.
-__global__ void __launch_bounds__(128) cam_segsum_kernel(const __nv_bfloat16* __restrict__ h,
+__global__ void __launch_bounds__(128) cam_segsum_kernel(const float* __restrict__ h,
                                                          const int* __restrict__ utt_B, const int* __restrict__ utt_T,
                                                          const int* __restrict__ seg_base, const int* __restrict__ seg_utt,
                                                          int seg_len, float* __restrict__ seg_sum) {
@@ -93,7 +97,7 @@ __global__ void __launch_bounds__(128) cam_segsum_kernel(const __nv_bfloat16* __
   const int B = utt_B[u], T = utt_T[u];
   const int t0 = s * seg_len, t1 = min(T, t0 + seg_len);
   float a = 0.f;
-  for (int t = t0; t < t1; ++t) a += __bfloat162float(h[(size_t)(B + t) * 128 + c]);
+  for (int t = t0; t < t1; ++t) a += h[(size_t)(B + t) * 128 + c];
   seg_sum[(size_t)g * 128 + c] = a;
 }
 

@@ -60,6 +60,8 @@ struct GemmEpi {
   const int* row_idx = nullptr;    // [M] or null: row_idx == -1 -> row written as zero; -2 -> row not written
   const float* row_gate = nullptr; // [*, N] or null: multiply by row_gate[row_idx[row] * N + n] (CAM mask)
   const __nv_bfloat16* resid = nullptr;  // EPI_BF16 only: bf16 tensor (same rows / ldo / col_off as out) added before act
+  const float* resid_f32 = nullptr;      // fp32 modes: fp32 tensor (same rows / ldo / col_off as out) added before act
+  int round_tf32 = 0;                    // fp32 modes: round the stored value to tf32 (operand of a later tf32 GEMM)
   // output row remap: out_row = (row / remap_q) * remap_fp + row % remap_q + remap_add   (remap_q == 0: identity)
   int remap_q = 0, remap_fp = 0, remap_add = 0;
 };
@@ -68,6 +70,7 @@ struct GemmArgs {
   CUtensorMap tmap_a;
   CUtensorMap tmap_b;
   int M = 0, N = 0;
+  int tf32 = 0;  // 0: bf16 operands, K blocks of 64 elements; 1: fp32 operands used as tf32, K blocks of 32 elements
   int nseg = 0;
   GemmSeg seg[kMaxSeg];
   GemmEpi epi;
@@ -75,6 +78,7 @@ struct GemmArgs {
 
 // Encode a 2-D bf16 row-major [rows, cols] tensor map (ld in elements) with a {64, box_rows} box, 128B swizzle.
 int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows);
+int make_tmap_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows);
 int gemm_block_n(int N);  // tile width the launcher picks for this N (32, 128 or 256)
 int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st);
 

@@ -24,9 +24,12 @@ constexpr int BK = 64;
 constexpr int kThreads = 256;
 constexpr int kEpiThreads = 128;
 
+// BN = 256 (the S3 encoder's big GEMMs) owns the SM; the narrow tiles of CAMPPlus (BN = 128 / 32) have short K loops
+// and latency-bound epilogues, so two CTAs share an SM and overlap each other's epilogue with their main loops.
 template <int BN>
 struct Cfg {
-  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kCtasPerSm = BN == 256 ? 1 : 2;
+  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 3 : 4);
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -43,9 +46,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int BN>
-__global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ GemmArgs args) {
+// TF32 = false: bf16 operands, 64-element K blocks.  TF32 = true: fp32 data consumed as tf32, 32-element K blocks
+// (both are 128-byte rows, so tiles, swizzle and descriptors are identical).
+template <int BN, bool TF32>
+__global__ void __launch_bounds__(kThreads, Cfg<BN>::kCtasPerSm) gemm_kernel(const __grid_constant__ GemmArgs args) {
   using C = Cfg<BN>;
+  constexpr int BKE = TF32 ? 32 : 64;  // K elements per block
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
@@ -100,8 +106,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             uint8_t* a_dst = tiles + stage * C::kStageBytes;
             uint8_t* b_dst = a_dst + C::kABytes;
             ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes);
-            ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BK, m0 + sg.a_row_off);
-            ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BK, n0);
+            ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
+            ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -110,7 +116,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(BM, BN);
+      constexpr uint32_t idesc = TF32 ? ptx::make_idesc_tf32(BM, BN) : ptx::make_idesc_bf16(BM, BN);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -130,7 +136,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             const uint64_t db = ptx::make_desc_sw128(a_addr + C::kABytes);
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
-              ptx::mma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              if (TF32) ptx::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              else ptx::mma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
               accumulate = 1;
             }
             ptx::mma_commit(&empty_bar[stage]);
@@ -199,10 +206,18 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
               }
             }
           }
+          if (e.resid_f32) {
+            const float4* rp = reinterpret_cast<const float4*>(e.resid_f32 + orow * e.ldo + col);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 w = __ldg(rp + j);
+              rs[4 * j] = w.x; rs[4 * j + 1] = w.y; rs[4 * j + 2] = w.z; rs[4 * j + 3] = w.w;
+            }
+          }
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             float t = __uint_as_float(v[j]) * s_scale[c * 32 + j] + s_bias[c * 32 + j];
-            if (e.resid) t += rs[j];
+            if (e.resid || e.resid_f32) t += rs[j];
             if (e.act == ACT_GELU) t = gelu_erf(t);
             else if (e.act == ACT_RELU) t = fmaxf(t, 0.0f);
             x[j] = t;
@@ -246,6 +261,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
               }
             }
           } else {
+            if (e.round_tf32) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) x[j] = ptx::round_tf32(x[j]);
+            }
             float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow * e.ldo + col);
             if (e.mode == EPI_F32_ADD) {
 #pragma unroll
@@ -291,17 +310,18 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
-template <int BN>
+template <int BN, bool TF32>
 int launch_bn(const GemmArgs& a, int num_sms, cudaStream_t st) {
   using C = Cfg<BN>;
   static bool configured = false;
   if (!configured) {
-    FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     configured = true;
   }
   const int tiles = ((a.M + BM - 1) / BM) * (a.N / BN);
-  const int grid = tiles < num_sms ? tiles : num_sms;
-  gemm_kernel<BN><<<grid, kThreads, C::kSmemBytes, st>>>(a);
+  const int slots = num_sms * C::kCtasPerSm;
+  const int grid = tiles < slots ? tiles : slots;
+  gemm_kernel<BN, TF32><<<grid, kThreads, C::kSmemBytes, st>>>(a);
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }
@@ -325,6 +345,23 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t c
   return FY_OK;
 }
 
+int make_tmap_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  FY_CHECK(enc != nullptr, FY_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  FY_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 4) % 16 == 0, FY_ERR_ARG,
+           "tensor map base/stride must be 16-byte aligned (ld=%llu)", (unsigned long long)ld);
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 4};
+  cuuint32_t box[2] = {32, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  FY_CHECK(r == CUDA_SUCCESS, FY_ERR_CUDA, "cuTensorMapEncodeTiled(f32) failed with %d (rows=%llu cols=%llu ld=%llu)",
+           (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld);
+  return FY_OK;
+}
+
 int gemm_block_n(int N) {
   if (N % 256 == 0) return 256;
   if (N % 128 == 0) return 128;
@@ -336,9 +373,9 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st) {
   FY_CHECK(a.M > 0 && a.nseg > 0 && a.nseg <= kMaxSeg, FY_ERR_ARG, "bad GEMM shape M=%d nseg=%d", a.M, a.nseg);
   FY_CHECK(a.epi.out != nullptr && a.epi.ldo > 0, FY_ERR_ARG, "GEMM epilogue has no output");
   switch (gemm_block_n(a.N)) {
-    case 256: return launch_bn<256>(a, num_sms, st);
-    case 128: return launch_bn<128>(a, num_sms, st);
-    case 32: return launch_bn<32>(a, num_sms, st);
+    case 256: return a.tf32 ? launch_bn<256, true>(a, num_sms, st) : launch_bn<256, false>(a, num_sms, st);
+    case 128: return a.tf32 ? launch_bn<128, true>(a, num_sms, st) : launch_bn<128, false>(a, num_sms, st);
+    case 32: return a.tf32 ? launch_bn<32, true>(a, num_sms, st) : launch_bn<32, false>(a, num_sms, st);
     default: FY_CHECK(false, FY_ERR_ARG, "GEMM N=%d must be a multiple of 32", a.N);
   }
   return FY_OK;

@@ -46,17 +46,17 @@ def main():
         x = feat.unsqueeze(0).permute(0, 2, 1).unsqueeze(1)
         h = m.head
         a = Fn.relu(h.bn1(h.conv1(x)))            # [1,32,80,T]
-        got = bf(L[2], R100 * 82 * 32).view(R100, 82, 32)[2:2 + T, 1:81]   # [T,80,32]
+        got = f32(L[2], R100 * 82 * 32).view(R100, 82, 32)[2:2 + T, 1:81]   # [T,80,32]
         print("stem", rel(got, a[0].permute(2, 1, 0)))
         names = [(5, 42, 40), (6, 42, 40), (9, 22, 20), (10, 22, 20)]
         for i, blk in enumerate(h.blocks):
             a = blk(a)
             off, fp, f = names[i]
-            got = bf(L[off], R100 * fp * 32).view(R100, fp, 32)
+            got = f32(L[off], R100 * fp * 32).view(R100, fp, 32)
             print(f"res{i}", rel(got[2:2 + T, 1:1 + f], a[0].permute(2, 1, 0)),
                   "pads", float(got[:, 0].abs().max()), float(got[:, fp - 1].abs().max()), float(got[:2].abs().max()), float(got[2 + T:].abs().max()))
         a = Fn.relu(h.bn2(h.conv2(a)))             # [1,32,10,T]
-        got = bf(L[11], R100 * 320).view(R100, 10, 32)
+        got = f32(L[11], R100 * 320).view(R100, 10, 32)
         print("fcm", rel(got[2:2 + T], a[0].permute(2, 1, 0)), "guards", float(got[:2].abs().max()), float(got[2 + T:].abs().max()))
         a = a.reshape(1, 320, T)
         a = m.tdnn_nl(m.tdnn(a))                   # [1,128,T2]
