@@ -45,7 +45,10 @@ struct GemmSeg {
   int nkb;        // number of 64-wide K blocks
 };
 
-enum EpiMode { EPI_BF16 = 0, EPI_F32_ADD = 1, EPI_F32_STORE = 2 };
+// EPI_QKV_ROPE: the fused q|k|v projection of the S3 encoder.  Column block n0 / rope_D selects q, k or v; q and k get
+// bias, rotary embedding (rotate-half inside each 64-wide head) and the d^-1/4 scale, v gets bias only; all three are
+// written as bf16 hi | lo operands for the attention / FSMN kernels (out = q, out2 = k, out3 = v).
+enum EpiMode { EPI_BF16 = 0, EPI_F32_ADD = 1, EPI_F32_STORE = 2, EPI_QKV_ROPE = 3 };
 enum EpiAct { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
 
 struct GemmEpi {
@@ -62,6 +65,14 @@ struct GemmEpi {
   const __nv_bfloat16* resid = nullptr;  // EPI_BF16 only: bf16 tensor (same rows / ldo / col_off as out) added before act
   const float* resid_f32 = nullptr;      // fp32 modes: fp32 tensor (same rows / ldo / col_off as out) added before act
   int round_tf32 = 0;                    // fp32 modes: round the stored value to tf32 (operand of a later tf32 GEMM)
+  // EPI_QKV_ROPE only
+  void* out2 = nullptr;
+  void* out3 = nullptr;
+  const float* rope_cos = nullptr;   // [positions, 64], both halves equal
+  const float* rope_sin = nullptr;
+  const int* rope_pos = nullptr;     // [M] position of each row inside its utterance (-1 on guard rows)
+  int rope_D = 0;                    // d_model (columns per projection)
+  float rope_scale = 1.0f;
   // output row remap: out_row = (row / remap_q) * remap_fp + row % remap_q + remap_add   (remap_q == 0: identity)
   int remap_q = 0, remap_fp = 0, remap_add = 0;
 };

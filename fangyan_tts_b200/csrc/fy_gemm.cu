@@ -21,8 +21,11 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kThreads = 256;
-constexpr int kEpiThreads = 128;
+// 4 control warps (TMA producer, MMA issuer, TMEM allocator, spare) + the epilogue warps.  BN = 256 tiles get two
+// epilogue warpgroups, each draining one half of the accumulator's columns, so the erf-GELU / hi-lo-split epilogues
+// of the S3 GEMMs stay hidden behind the next tile's main loop; narrow tiles keep one warpgroup (two CTAs per SM).
+template <int BN> constexpr int epi_warps() { return BN == 256 ? 8 : 4; }
+template <int BN> constexpr int cta_threads() { return 128 + 32 * epi_warps<BN>(); }
 
 // BN = 256 (the S3 encoder's big GEMMs) owns the SM; the narrow tiles of CAMPPlus (BN = 128 / 32) have short K loops
 // and latency-bound epilogues, so two CTAs share an SM and overlap each other's epilogue with their main loops.
@@ -39,7 +42,20 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 2 * BN * 4 + 1024;
 };
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// Exact (erf) GELU, x * Phi(x), with erfc from Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, below fp32 rounding of
+// the product): Phi(x) = h for x < 0 and 1 - h otherwise, h = 0.5 * poly(t) * exp(-x^2 / 2), t = 1 / (1 + p |x| / sqrt 2).
+// Evaluating h directly avoids the 1 + erf cancellation for negative x and costs two MUFU ops instead of erff's ~30
+// instructions, which is what kept the fc1 epilogue (5120 columns of GELU + hi/lo split) longer than its main loop.
+__device__ __forceinline__ float gelu_erf(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  float p = fmaf(t, 1.061405429f, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  const float h = 0.5f * p * t * __expf(-z * z);
+  return x * (x < 0.0f ? h : 1.0f - h);
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -49,9 +65,10 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // TF32 = false: bf16 operands, 64-element K blocks.  TF32 = true: fp32 data consumed as tf32, 32-element K blocks
 // (both are 128-byte rows, so tiles, swizzle and descriptors are identical).
 template <int BN, bool TF32>
-__global__ void __launch_bounds__(kThreads, Cfg<BN>::kCtasPerSm) gemm_kernel(const __grid_constant__ GemmArgs args) {
+__global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_kernel(const __grid_constant__ GemmArgs args) {
   using C = Cfg<BN>;
   constexpr int BKE = TF32 ? 32 : 64;  // K elements per block
+  constexpr int kEpiThreads = 32 * epi_warps<BN>();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* tiles = smem;
@@ -149,9 +166,11 @@ __global__ void __launch_bounds__(kThreads, Cfg<BN>::kCtasPerSm) gemm_kernel(con
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue (warps 4..7 = TMEM lane quarters 0..3) =====================
-    const int q = warp - 4;
+    // ===================== epilogue (warp w drains TMEM lane quarter w % 4; warps 8..11 take the upper columns) ====
+    const int q = warp & 3;
     const int et = threadIdx.x - 128;
+    constexpr int kChunks = BN / 32 / (epi_warps<BN>() / 4);   // 32-column chunks per warp
+    const int c_begin = ((warp - 4) >> 2) * kChunks;
     const GemmEpi& e = args.epi;
     int as = 0;
     uint32_t aphase = 0;
@@ -160,12 +179,12 @@ __global__ void __launch_bounds__(kThreads, Cfg<BN>::kCtasPerSm) gemm_kernel(con
       const int m0 = (tile / num_n) * BM;
       const int n0 = (tile % num_n) * BN;
       if (n0 != staged_n0) {  // per-column scale / bias of this N block -> shared memory (uniform branch)
-        asm volatile("bar.sync 1, 128;\n" ::: "memory");
+        asm volatile("bar.sync 1, %0;\n" ::"n"(kEpiThreads) : "memory");
         for (int i = et; i < BN; i += kEpiThreads) {
           s_scale[i] = e.scale ? __ldg(e.scale + n0 + i) : 1.0f;
           s_bias[i] = e.bias ? __ldg(e.bias + n0 + i) : 0.0f;
         }
-        asm volatile("bar.sync 1, 128;\n" ::: "memory");
+        asm volatile("bar.sync 1, %0;\n" ::"n"(kEpiThreads) : "memory");
         staged_n0 = n0;
       }
       const int row = m0 + q * 32 + lane;
@@ -177,15 +196,85 @@ __global__ void __launch_bounds__(kThreads, Cfg<BN>::kCtasPerSm) gemm_kernel(con
       const size_t orow = e.remap_q ? (size_t)(row / e.remap_q) * e.remap_fp + row % e.remap_q + e.remap_add : (size_t)row;
       uint4 rpre[4];
       if (e.resid && row_ok) {  // first chunk of the residual: issue the loads before waiting for the accumulator
-        const uint4* rp = reinterpret_cast<const uint4*>(e.resid + orow * e.ldo + (size_t)e.col_off + n0);
+        const uint4* rp = reinterpret_cast<const uint4*>(e.resid + orow * e.ldo + (size_t)e.col_off + n0 + c_begin * 32);
 #pragma unroll
         for (int j = 0; j < 4; ++j) rpre[j] = __ldg(rp + j);
       }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+      if (BN == 256 && e.mode == EPI_QKV_ROPE) {
+        // 64-column heads: columns [h*64, +32) pair with [h*64 + 32, +32).  Drained 16 + 16 columns at a time.
+        const int which = n0 / e.rope_D;
+        const int cbase = n0 - which * e.rope_D;
+        __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(which == 0 ? e.out : (which == 1 ? e.out2 : e.out3));
+        __nv_bfloat16* o = ob + (size_t)row * e.ldo + cbase;
+        int pos = row_ok ? __ldg(e.rope_pos + row) : 0;
+        if (pos < 0) pos = 0;
+        const float* ct = e.rope_cos + (size_t)pos * 64;
+        const float* sn = e.rope_sin + (size_t)pos * 64;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+        for (int hs = 0; hs < kChunks; ++hs) {           // kChunks / 2 heads x 2 sub-chunks of 16 pairs
+          const int ca = c_begin * 32 + (hs >> 1) * 64 + (hs & 1) * 16;   // tile-local column of the first half
+          uint32_t va[16], vb[16];
+          ptx::tmem_ld_32x16(t_row + ca, va);
+          ptx::tmem_ld_32x16(t_row + ca + 32, vb);
+          ptx::tmem_ld_wait();
+          if (row_ok) {
+            float xa[16], xb[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              xa[j] = __uint_as_float(va[j]) + s_bias[ca + j];
+              xb[j] = __uint_as_float(vb[j]) + s_bias[ca + 32 + j];
+            }
+            if (which < 2) {
+              const int d0 = (hs & 1) * 16;
+#pragma unroll
+              for (int j4 = 0; j4 < 4; ++j4) {
+                const float4 c4 = __ldg(reinterpret_cast<const float4*>(ct + d0) + j4);
+                const float4 s4 = __ldg(reinterpret_cast<const float4*>(sn + d0) + j4);
+                const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float a = xa[4 * j4 + k], b = xb[4 * j4 + k];
+                  xa[4 * j4 + k] = (a * cc[k] - b * ss[k]) * e.rope_scale;
+                  xb[4 * j4 + k] = (b * cc[k] + a * ss[k]) * e.rope_scale;
+                }
+              }
+            }
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              float* xs = half ? xb : xa;
+              uint4* dhi = reinterpret_cast<uint4*>(o + ca + half * 32);
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                uint4 w;
+                w.x = pack_bf16(xs[8 * j], xs[8 * j + 1]); w.y = pack_bf16(xs[8 * j + 2], xs[8 * j + 3]);
+                w.z = pack_bf16(xs[8 * j + 4], xs[8 * j + 5]); w.w = pack_bf16(xs[8 * j + 6], xs[8 * j + 7]);
+                dhi[j] = w;
+              }
+              if (e.lo_col_off >= 0) {
+                uint4* dlo = reinterpret_cast<uint4*>(o + e.lo_col_off + ca + half * 32);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) xs[j] -= __bfloat162float(__float2bfloat16_rn(xs[j]));
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                  uint4 w;
+                  w.x = pack_bf16(xs[8 * j], xs[8 * j + 1]); w.y = pack_bf16(xs[8 * j + 2], xs[8 * j + 3]);
+                  w.z = pack_bf16(xs[8 * j + 4], xs[8 * j + 5]); w.w = pack_bf16(xs[8 * j + 6], xs[8 * j + 7]);
+                  dlo[j] = w;
+                }
+              }
+            }
+          }
+        }
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(&tempty_bar[as]);
+        if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
+        continue;
+      }
+#pragma unroll 1
+      for (int c = c_begin; c < c_begin + kChunks; ++c) {
         uint32_t v[32];
         ptx::tmem_ld_32x32(t_row + c * 32, v);
         ptx::tmem_ld_wait();
@@ -197,7 +286,7 @@ __global__ void __launch_bounds__(kThreads, Cfg<BN>::kCtasPerSm) gemm_kernel(con
             const uint4* rp = reinterpret_cast<const uint4*>(e.resid + orow * e.ldo + col);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const uint4 w = c == 0 ? rpre[j] : __ldg(rp + j);
+              const uint4 w = c == c_begin ? rpre[j] : __ldg(rp + j);
               const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
@@ -321,7 +410,7 @@ int launch_bn(const GemmArgs& a, int num_sms, cudaStream_t st) {
   const int tiles = ((a.M + BM - 1) / BM) * (a.N / BN);
   const int slots = num_sms * C::kCtasPerSm;
   const int grid = tiles < slots ? tiles : slots;
-  gemm_kernel<BN, TF32><<<grid, kThreads, C::kSmemBytes, st>>>(a);
+  gemm_kernel<BN, TF32><<<grid, cta_threads<BN>(), C::kSmemBytes, st>>>(a);
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }

@@ -1,5 +1,5 @@
-// Row-wise kernels of the S3 tokenizer encoder (rows A9/A10): layout change, LayerNorm, RoPE + split, FSMN memory,
-// FSQ.  All HBM-bound; activations are fp32 in the residual stream and bf16 (hi | lo) as tensor-core operands.
+// Row-wise kernels of the S3 tokenizer encoder (rows A9/A10): layout change, LayerNorm, FSMN memory, FSQ (RoPE and
+// the q/k/v operand split live in the QKV GEMM's epilogue, fy_gemm.cu).  All HBM-bound; activations are fp32 in the residual stream and bf16 (hi | lo) as tensor-core operands.
 #pragma once
 #include "fy_common.cuh"
 
@@ -91,114 +91,80 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
   }
 }
 
-// qkv fp32 [rows, 3D] -> q, k (RoPE, rotate-half, then * scale) and v as bf16 [rows, D * W] (hi | lo).
-// One thread per (row, head, d < DH/2) handles the pair (d, d + DH/2) of q and k and two v values.
-template <bool SPLIT>
-__global__ void __launch_bounds__(256) rope_split_kernel(const float* __restrict__ qkv, const int* __restrict__ row_pos,
-                                                         const float* __restrict__ cosT, const float* __restrict__ sinT,
-                                                         int rows, int D, int DH, float scale,
-                                                         __nv_bfloat16* __restrict__ q, __nv_bfloat16* __restrict__ k,
-                                                         __nv_bfloat16* __restrict__ v) {
-  const int half = DH / 2;
-  const int per_row = D / 2;
-  const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (idx >= (size_t)rows * per_row) return;
-  const int row = (int)(idx / per_row);
-  const int r = (int)(idx % per_row);
-  const int h = r / half, d = r % half;
-  const int c0 = h * DH + d, c1 = c0 + half;
-  int pos = __ldg(row_pos + row);
-  if (pos < 0) pos = 0;
-  const float cs0 = __ldg(cosT + (size_t)pos * DH + d), sn0 = __ldg(sinT + (size_t)pos * DH + d);
-  const float cs1 = __ldg(cosT + (size_t)pos * DH + d + half), sn1 = __ldg(sinT + (size_t)pos * DH + d + half);
-  const float* src = qkv + (size_t)row * 3 * D;
-  const int LD = SPLIT ? 2 * D : D;
-  const size_t o = (size_t)row * LD;
-  __nv_bfloat16 hi, lo;
-  {
-    const float a = src[c0], b = src[c1];
-    split_bf16((a * cs0 - b * sn0) * scale, hi, lo);
-    q[o + c0] = hi; if (SPLIT) q[o + D + c0] = lo;
-    split_bf16((b * cs1 + a * sn1) * scale, hi, lo);
-    q[o + c1] = hi; if (SPLIT) q[o + D + c1] = lo;
-  }
-  {
-    const float a = src[D + c0], b = src[D + c1];
-    split_bf16((a * cs0 - b * sn0) * scale, hi, lo);
-    k[o + c0] = hi; if (SPLIT) k[o + D + c0] = lo;
-    split_bf16((b * cs1 + a * sn1) * scale, hi, lo);
-    k[o + c1] = hi; if (SPLIT) k[o + D + c1] = lo;
-  }
-  {
-    split_bf16(src[2 * D + c0], hi, lo);
-    v[o + c0] = hi; if (SPLIT) v[o + D + c0] = lo;
-    split_bf16(src[2 * D + c1], hi, lo);
-    v[o + c1] = hi; if (SPLIT) v[o + D + c1] = lo;
-  }
-}
-
-// FSMN memory: x[row, c] += v[row, c] + sum_j w[j][c] * v[row + j - pad, c] over rows of the same utterance.
-// v is the fp32 value projection inside qkv (column offset 2D).  A block stages a (64 + KS - 1) x 64 tile of v in
-// shared memory (each value leaves L2 once); a thread owns 8 consecutive rows x 4 channels and slides an
-// 8-row register window over the taps, so shared memory is read ~3 times per tap instead of 2 per tap per output.
-// grid: (ceil(rows / 64), D / 64), block 128.
+// FSMN memory: x[row, c] += v[row, c] + sum_j w[j][c] * v[row + j - pad, c], taps confined to the row's utterance.
+// v is the value projection as written by the fused QKV epilogue: bf16 [rows, ldv] with hi at column c and (SPLIT)
+// lo at lo_off + c; hi + lo restores it to 2^-17.  One block = one 64-row tile of ONE utterance (the attention tile
+// list is reused) x 64 channels: the tile plus its 15-row halos, clipped to the utterance and zero-filled outside, is
+// staged in shared memory once, so the tap loop has no utterance tests.  A thread owns 8 consecutive rows x 4
+// channels and slides an 8-row register window over the 31 taps (one LDS.128 of v and one of w per 32 FMAs); its
+// residual-stream values are prefetched into L2 before the tap loop so the final read-modify-write is short.
+// grid: (n_tiles, D / 64), block 128.
 constexpr int kFsmnRows = 64, kFsmnCols = 64, kFsmnMaxK = 31, kFsmnPerThread = 8;
-template <int KS>
-__global__ void __launch_bounds__(128) fsmn_kernel(const float* __restrict__ qkv, const int* __restrict__ row_utt,
-                                                   const float* __restrict__ w /* [KS][D] tap-major */, int rows, int D,
-                                                   float* __restrict__ x) {
+template <int KS, bool SPLIT>
+__global__ void __launch_bounds__(128, 4) fsmn_kernel(const __nv_bfloat16* __restrict__ v, int ldv, int lo_off,
+                                                      const int2* __restrict__ tiles, const int* __restrict__ utt_P,
+                                                      const int* __restrict__ utt_L,
+                                                      const float* __restrict__ w /* [KS][D] tap-major */, int D,
+                                                      float* __restrict__ x) {
   constexpr int kSpan = kFsmnRows + KS - 1;
   constexpr int kPad = (KS - 1) / 2;
   __shared__ float4 sv[kSpan][kFsmnCols / 4];
   __shared__ float4 sw[KS][kFsmnCols / 4];
-  __shared__ int sutt[kSpan];
-  const int r0 = blockIdx.x * kFsmnRows, c0 = blockIdx.y * kFsmnCols;
-  const size_t ldv = (size_t)3 * D;
+  const int2 tl = tiles[blockIdx.x];
+  const int P = utt_P[tl.x], L = utt_L[tl.x], t0 = tl.y;
+  const int c0 = blockIdx.y * kFsmnCols;
+  const int c4 = threadIdx.x & 15;
+  const int r0 = (threadIdx.x >> 4) * kFsmnPerThread;   // first output row of this thread inside the tile
+  // pull this thread's residual-stream values into L2 now; they are read after the tap loop
+#pragma unroll
+  for (int i = 0; i < kFsmnPerThread; ++i) {
+    const int t = t0 + r0 + i;
+    if (t < L) asm volatile("prefetch.global.L2 [%0];\n" ::"l"(x + (size_t)(P + t) * D + c0 + c4 * 4));
+  }
   for (int i = threadIdx.x; i < kSpan * 16; i += 128) {
-    const int rr = i >> 4, c4 = i & 15;
-    const int row = r0 - kPad + rr;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row >= 0 && row < rows) v = *reinterpret_cast<const float4*>(qkv + (size_t)row * ldv + 2 * D + c0 + c4 * 4);
-    sv[rr][c4] = v;
-    if (c4 == 0) sutt[rr] = (row >= 0 && row < rows) ? __ldg(row_utt + row) : -1;
+    const int rr = i >> 4, cc = i & 15;
+    const int t = t0 - kPad + rr;
+    float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t >= 0 && t < L) {
+      const __nv_bfloat16* src = v + (size_t)(P + t) * ldv + c0 + cc * 4;
+      const uint2 h = __ldg(reinterpret_cast<const uint2*>(src));
+      val.x = __uint_as_float(h.x << 16); val.y = __uint_as_float(h.x & 0xffff0000u);
+      val.z = __uint_as_float(h.y << 16); val.w = __uint_as_float(h.y & 0xffff0000u);
+      if (SPLIT) {
+        const uint2 l = __ldg(reinterpret_cast<const uint2*>(src + lo_off));
+        val.x += __uint_as_float(l.x << 16); val.y += __uint_as_float(l.x & 0xffff0000u);
+        val.z += __uint_as_float(l.y << 16); val.w += __uint_as_float(l.y & 0xffff0000u);
+      }
+    }
+    sv[rr][cc] = val;
   }
   for (int i = threadIdx.x; i < KS * 16; i += 128)
     sw[i >> 4][i & 15] = __ldg(reinterpret_cast<const float4*>(w + (size_t)(i >> 4) * D + c0 + (i & 15) * 4));
   __syncthreads();
-  const int c4 = threadIdx.x & 15;
-  const int t0 = (threadIdx.x >> 4) * kFsmnPerThread;   // first output row of this thread inside the tile
   float4 acc[kFsmnPerThread];
-  int uo[kFsmnPerThread];
 #pragma unroll
-  for (int i = 0; i < kFsmnPerThread; ++i) {
-    acc[i] = sv[t0 + i + kPad][c4];                     // identity term
-    uo[i] = sutt[t0 + i + kPad];
-  }
-  float4 win[kFsmnPerThread];                            // rows t0 + j .. t0 + j + 7 of the staged tile
-  int wu[kFsmnPerThread];
+  for (int i = 0; i < kFsmnPerThread; ++i) acc[i] = sv[r0 + i + kPad][c4];   // identity term
+  float4 win[kFsmnPerThread];                                                // staged rows r0 + j .. r0 + j + 7
 #pragma unroll
-  for (int i = 0; i < kFsmnPerThread - 1; ++i) { win[i] = sv[t0 + i][c4]; wu[i] = sutt[t0 + i]; }
+  for (int i = 0; i < kFsmnPerThread - 1; ++i) win[i] = sv[r0 + i][c4];
 #pragma unroll
   for (int j = 0; j < KS; ++j) {
-    win[(j + kFsmnPerThread - 1) % kFsmnPerThread] = sv[t0 + j + kFsmnPerThread - 1][c4];
-    wu[(j + kFsmnPerThread - 1) % kFsmnPerThread] = sutt[t0 + j + kFsmnPerThread - 1];
+    win[(j + kFsmnPerThread - 1) % kFsmnPerThread] = sv[r0 + j + kFsmnPerThread - 1][c4];
     const float4 ww = sw[j][c4];
 #pragma unroll
     for (int i = 0; i < kFsmnPerThread; ++i) {
       const float4 vv = win[(i + j) % kFsmnPerThread];
-      if (wu[(i + j) % kFsmnPerThread] == uo[i]) {
-        acc[i].x += ww.x * vv.x; acc[i].y += ww.y * vv.y; acc[i].z += ww.z * vv.z; acc[i].w += ww.w * vv.w;
-      }
+      acc[i].x = fmaf(ww.x, vv.x, acc[i].x); acc[i].y = fmaf(ww.y, vv.y, acc[i].y);
+      acc[i].z = fmaf(ww.z, vv.z, acc[i].z); acc[i].w = fmaf(ww.w, vv.w, acc[i].w);
     }
   }
 #pragma unroll
   for (int i = 0; i < kFsmnPerThread; ++i) {
-    const int row = r0 + t0 + i;
-    if (row < rows && uo[i] >= 0) {
-      float4* xp = reinterpret_cast<float4*>(x + (size_t)row * D + c0 + c4 * 4);
-      float4 xv = *xp;
-      xv.x += acc[i].x; xv.y += acc[i].y; xv.z += acc[i].z; xv.w += acc[i].w;
-      *xp = xv;
+    const int t = t0 + r0 + i;
+    if (t < L) {
+      float4 o = *reinterpret_cast<const float4*>(x + (size_t)(P + t) * D + c0 + c4 * 4);
+      o.x += acc[i].x; o.y += acc[i].y; o.z += acc[i].z; o.w += acc[i].w;
+      *reinterpret_cast<float4*>(x + (size_t)(P + t) * D + c0 + c4 * 4) = o;
     }
   }
 }

@@ -111,7 +111,7 @@ size_t align_up(size_t x, size_t a = 1024) { return (x + a - 1) / a * a; }
 
 struct Layout {  // per-call sizes derived from the frame counts
   int n_utts = 0, Rtok = 0, R1 = 0, Rmel = 0, n_attn_tiles = 0, Tmax = 0;
-  size_t o_meta, o_mel, o_c1, o_x, o_xn, o_qkv, o_q, o_k, o_v, o_att, o_h, total;
+  size_t o_meta, o_mel, o_c1, o_x, o_xn, o_q, o_k, o_v, o_att, o_h, total;
   // meta sub-offsets (ints)
   size_t m_P, m_L, m_row1, m_rutt, m_rpos, m_tiles, meta_ints;
 };
@@ -141,7 +141,6 @@ Layout make_layout(const fy_s3_config& c, int W, int n_utts, int rtok, int n_til
   l.o_c1 = o; o = align_up(o + (size_t)l.R1 * D * W * 2);
   l.o_x = o; o = align_up(o + (size_t)rtok * D * 4);
   l.o_xn = o; o = align_up(o + (size_t)rtok * D * W * 2);
-  l.o_qkv = o; o = align_up(o + (size_t)rtok * 3 * D * 4);
   l.o_q = o; o = align_up(o + (size_t)rtok * D * W * 2);
   l.o_k = o; o = align_up(o + (size_t)rtok * D * W * 2);
   l.o_v = o; o = align_up(o + (size_t)rtok * D * W * 2);
@@ -368,7 +367,6 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   __nv_bfloat16* b_c1 = reinterpret_cast<__nv_bfloat16*>(base + lay.o_c1);
   float* b_x = reinterpret_cast<float*>(base + lay.o_x);
   __nv_bfloat16* b_xn = reinterpret_cast<__nv_bfloat16*>(base + lay.o_xn);
-  float* b_qkv = reinterpret_cast<float*>(base + lay.o_qkv);
   __nv_bfloat16* b_q = reinterpret_cast<__nv_bfloat16*>(base + lay.o_q);
   __nv_bfloat16* b_k = reinterpret_cast<__nv_bfloat16*>(base + lay.o_k);
   __nv_bfloat16* b_v = reinterpret_cast<__nv_bfloat16*>(base + lay.o_v);
@@ -427,18 +425,16 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       GemmArgs g;
       g.tmap_a = m_xn; g.tmap_b = Lw.m_qkv; g.M = Rtok; g.N = 3 * D;
       add_products(g, W, 0, 0, 0, D, D, D);
-      g.epi.mode = EPI_F32_STORE; g.epi.out = b_qkv; g.epi.ldo = 3 * D; g.epi.bias = Lw.bqkv;
+      g.epi.mode = EPI_QKV_ROPE; g.epi.out = b_q; g.epi.out2 = b_k; g.epi.out3 = b_v; g.epi.ldo = D * W;
+      g.epi.lo_col_off = W == 2 ? D : -1; g.epi.bias = Lw.bqkv;
+      g.epi.rope_cos = p->rope_cos; g.epi.rope_sin = p->rope_sin; g.epi.rope_pos = d_rpos; g.epi.rope_D = D;
+      g.epi.rope_scale = qk_scale;
       FY_TRY(run_gemm(c, g, 2.0 * vtok * 3 * D * D));
     }
     {
-      const size_t n = (size_t)Rtok * (D / 2);
-      const int grid = (int)((n + 255) / 256);
-      if (W == 2) s3k::rope_split_kernel<true><<<grid, 256, 0, st>>>(b_qkv, d_rpos, p->rope_cos, p->rope_sin, Rtok, D, 64, qk_scale, b_q, b_k, b_v);
-      else s3k::rope_split_kernel<false><<<grid, 256, 0, st>>>(b_qkv, d_rpos, p->rope_cos, p->rope_sin, Rtok, D, 64, qk_scale, b_q, b_k, b_v);
-    }
-    {
-      dim3 fg((Rtok + s3k::kFsmnRows - 1) / s3k::kFsmnRows, D / s3k::kFsmnCols);
-      s3k::fsmn_kernel<31><<<fg, 128, 0, st>>>(b_qkv, d_rutt, Lw.fsmn, Rtok, D, b_x);
+      dim3 fg(tiles, D / s3k::kFsmnCols);
+      if (W == 2) s3k::fsmn_kernel<31, true><<<fg, 128, 0, st>>>(b_v, D * W, D, d_tiles, d_P, d_L, Lw.fsmn, D, b_x);
+      else s3k::fsmn_kernel<31, false><<<fg, 128, 0, st>>>(b_v, D * W, D, d_tiles, d_P, d_L, Lw.fsmn, D, b_x);
     }
     {
       const int pi = prof_begin(c, PK_ATTN);
@@ -446,7 +442,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       if (W == 2) attn::attention_kernel<true><<<grid, attn::kThreads, attn::smem_bytes<true>(), st>>>(b_q, b_k, b_v, b_att, D * W, D, d_tiles, d_P, d_L);
       else attn::attention_kernel<false><<<grid, attn::kThreads, attn::smem_bytes<false>(), st>>>(b_q, b_k, b_v, b_att, D * W, D, d_tiles, d_P, d_L);
       prof_end(c, pi, attn_flops);
-      c->launches += 5;  // layernorm x2, rope, fsmn, attention
+      c->launches += 4;  // layernorm x2, fsmn, attention
     }
     FY_CUDA(cudaGetLastError());
     {
