@@ -8,20 +8,22 @@
 namespace fy {
 namespace camk {
 
+// Activations of this network are stored as IEEE fp16: the same 11-bit significand as tf32 at half the bytes.  Every
+// stored value is post-BatchNorm / post-gate (O(1..100)), far inside fp16's range.
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  __half2 v = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+__device__ __forceinline__ float2 unpack2(uint32_t u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
 
 // Stem: Conv2d(1, 32, 3x3, pad 1) + BN + ReLU over (freq, time).  feat is packed [frames, 80] fp32.
-// out: [R100, 82, 32] fp32 (rounded to tf32: it is the A operand of the first FCM GEMM) channels-last with zero
-// columns at p = 0 and p = 81 (buffer pre-zeroed).
+// out: [R100, 82, 32] fp16 channels-last with zero columns at p = 0 and p = 81 (buffer pre-zeroed).
 // rowsrc[r] = feat row of time row r or -1 for guard rows.  w: [32][3 (freq)][3 (time)].
 // grid = R100, block = 320 (80 freq x 4 groups of 8 channels).
 __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ feat, const int* __restrict__ rowsrc,
                                                    int R100, const float* __restrict__ w,
                                                    const float* __restrict__ scale, const float* __restrict__ shift,
-                                                   float* __restrict__ out) {
+                                                   __half* __restrict__ out) {
   const int r = blockIdx.x;
   const int src = rowsrc[r];
   if (src < 0) return;
@@ -51,11 +53,11 @@ __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ fea
     for (int i = 0; i < 3; ++i)
 #pragma unroll
       for (int j = 0; j < 3; ++j) a += sw[c * 9 + i * 3 + j] * x[i][j];
-    y[k] = ptx::round_tf32(fmaxf(a * sw[288 + c] + sw[320 + c], 0.f));
+    y[k] = fmaxf(a * sw[288 + c] + sw[320 + c], 0.f);
   }
-  float4* dst = reinterpret_cast<float4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8);
-  dst[0] = make_float4(y[0], y[1], y[2], y[3]);
-  dst[1] = make_float4(y[4], y[5], y[6], y[7]);
+  uint4 o;
+  o.x = pack2(y[0], y[1]); o.y = pack2(y[2], y[3]); o.z = pack2(y[4], y[5]); o.w = pack2(y[6], y[7]);
+  *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8) = o;
 }
 
 // mask[g] = -2 (skip) when slot g % Q is outside [lo, hi]; else -1 (write zero) on guard time rows; else 0
@@ -66,28 +68,29 @@ __global__ void pos_mask_kernel(const int* __restrict__ rowsrc, int R, int Q, in
   mask[g] = (p < lo || p > hi) ? -2 : (rowsrc[g / Q] >= 0 ? 0 : -1);
 }
 
-// y = tf32(relu(x * scale[c] + shift[c])) for c < C; x fp32 [R, ldx], y fp32 [R, ldy].  4 channels per thread.
-__global__ void __launch_bounds__(256) bnrelu_kernel(const float* __restrict__ x, int ldx, int R, int C,
+// y = fp16(relu(x * scale[c] + shift[c])) for c < C; x fp16 [R, ldx], y fp16 [R, ldy].  8 channels per thread.
+__global__ void __launch_bounds__(256) bnrelu_kernel(const __half* __restrict__ x, int ldx, int R, int C,
                                                      const float* __restrict__ scale, const float* __restrict__ shift,
-                                                     float* __restrict__ y, int ldy) {
-  const int per_row = C / 4;
+                                                     __half* __restrict__ y, int ldy) {
+  const int per_row = C / 8;
   const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
   if (idx >= (size_t)R * per_row) return;
-  const int r = (int)(idx / per_row), c = (int)(idx % per_row) * 4;
-  const float4 v = *reinterpret_cast<const float4*>(x + (size_t)r * ldx + c);
-  const float4 s = __ldg(reinterpret_cast<const float4*>(scale + c));
-  const float4 b = __ldg(reinterpret_cast<const float4*>(shift + c));
-  float4 o;
-  o.x = ptx::round_tf32(fmaxf(v.x * s.x + b.x, 0.f));
-  o.y = ptx::round_tf32(fmaxf(v.y * s.y + b.y, 0.f));
-  o.z = ptx::round_tf32(fmaxf(v.z * s.z + b.z, 0.f));
-  o.w = ptx::round_tf32(fmaxf(v.w * s.w + b.w, 0.f));
-  *reinterpret_cast<float4*>(y + (size_t)r * ldy + c) = o;
+  const int r = (int)(idx / per_row), c = (int)(idx % per_row) * 8;
+  const uint4 v = *reinterpret_cast<const uint4*>(x + (size_t)r * ldx + c);
+  const float4 s0 = __ldg(reinterpret_cast<const float4*>(scale + c)), s1 = __ldg(reinterpret_cast<const float4*>(scale + c + 4));
+  const float4 b0 = __ldg(reinterpret_cast<const float4*>(shift + c)), b1 = __ldg(reinterpret_cast<const float4*>(shift + c + 4));
+  const float2 a0 = unpack2(v.x), a1 = unpack2(v.y), a2 = unpack2(v.z), a3 = unpack2(v.w);
+  uint4 o;
+  o.x = pack2(fmaxf(a0.x * s0.x + b0.x, 0.f), fmaxf(a0.y * s0.y + b0.y, 0.f));
+  o.y = pack2(fmaxf(a1.x * s0.z + b0.z, 0.f), fmaxf(a1.y * s0.w + b0.w, 0.f));
+  o.z = pack2(fmaxf(a2.x * s1.x + b1.x, 0.f), fmaxf(a2.y * s1.y + b1.y, 0.f));
+  o.w = pack2(fmaxf(a3.x * s1.z + b1.z, 0.f), fmaxf(a3.y * s1.w + b1.w, 0.f));
+  *reinterpret_cast<uint4*>(y + (size_t)r * ldy + c) = o;
 }
 
-// CAM gate, step 1: per-segment column sums of h (fp32 [R50, 128], post BN+ReLU bottleneck).
+// CAM gate, step 1: per-segment column sums of h (fp16 [R50, 128], post BN+ReLU bottleneck).
 // One block of 128 threads per global segment g; seg_utt[g] = utterance, seg_base[u] = first segment of u.
-__global__ void __launch_bounds__(128) cam_segsum_kernel(const float* __restrict__ h,
+__global__ void __launch_bounds__(128) cam_segsum_kernel(const __half* __restrict__ h,
                                                          const int* __restrict__ utt_B, const int* __restrict__ utt_T,
                                                          const int* __restrict__ seg_base, const int* __restrict__ seg_utt,
                                                          int seg_len, float* __restrict__ seg_sum) {
@@ -97,7 +100,7 @@ __global__ void __launch_bounds__(128) cam_segsum_kernel(const float* __restrict
   const int B = utt_B[u], T = utt_T[u];
   const int t0 = s * seg_len, t1 = min(T, t0 + seg_len);
   float a = 0.f;
-  for (int t = t0; t < t1; ++t) a += h[(size_t)(B + t) * 128 + c];
+  for (int t = t0; t < t1; ++t) a += __half2float(h[(size_t)(B + t) * 128 + c]);
   seg_sum[(size_t)g * 128 + c] = a;
 }
 
@@ -139,8 +142,8 @@ __global__ void __launch_bounds__(128) cam_gate_kernel(const float* __restrict__
 }
 
 // Statistics pooling after BN+ReLU: stats[u] = [mean(1..C), std_unbiased(1..C)] over the utterance's rows.
-// x fp32 [R50, ldx]; one block per utterance, one thread per channel (C <= 512).
-__global__ void __launch_bounds__(512) stats_kernel(const float* __restrict__ x, int ldx, int C,
+// x fp16 [R50, ldx]; one block per utterance, one thread per channel (C <= 512).
+__global__ void __launch_bounds__(512) stats_kernel(const __half* __restrict__ x, int ldx, int C,
                                                     const int* __restrict__ utt_B, const int* __restrict__ utt_T,
                                                     const float* __restrict__ scale, const float* __restrict__ shift,
                                                     float* __restrict__ stats) {
@@ -149,11 +152,11 @@ __global__ void __launch_bounds__(512) stats_kernel(const float* __restrict__ x,
   const int B = utt_B[u], T = utt_T[u];
   const float s = scale[c], b = shift[c];
   float sum = 0.f;
-  for (int t = 0; t < T; ++t) sum += fmaxf(x[(size_t)(B + t) * ldx + c] * s + b, 0.f);
+  for (int t = 0; t < T; ++t) sum += fmaxf(__half2float(x[(size_t)(B + t) * ldx + c]) * s + b, 0.f);
   const float mean = sum / (float)T;
   float ss = 0.f;
   for (int t = 0; t < T; ++t) {
-    const float d = fmaxf(x[(size_t)(B + t) * ldx + c] * s + b, 0.f) - mean;
+    const float d = fmaxf(__half2float(x[(size_t)(B + t) * ldx + c]) * s + b, 0.f) - mean;
     ss += d * d;
   }
   stats[(size_t)u * 2 * C + c] = mean;

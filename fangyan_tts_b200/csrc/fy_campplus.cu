@@ -8,10 +8,10 @@
 // head keeps activations channels-last as [time row][freq position + 2 pads][32]; every 3x3 convolution is one
 // tcgen05 GEMM with one K-block per tap (row offset = dt * positions_per_row + df).
 //
-// Precision: every GEMM here is kind::tf32 on fp32 activations and weights that were rounded to tf32 (nearest) by
-// their producer, fp32 accumulate.  A single bf16 pass leaves the embedding at cosine 0.9998-0.99997 against the
-// fp32 oracle (60+ layers of 2^-9 operand rounding), below the 0.9999 gate; tf32's 2^-12 rounding clears it by two
-// orders of magnitude at 2/3 of the split-bf16 cost, with no hi/lo operand copies.
+// Precision: every GEMM here is kind::f16 on IEEE fp16 activations and weights, fp32 accumulate.  A single bf16 pass
+// leaves the embedding at cosine 0.9998-0.99997 against the fp32 oracle (60+ layers of 2^-9 operand rounding), below
+// the 0.9999 gate; fp16's 11-bit significand (the same as tf32's) clears it by two orders of magnitude at one third
+// of the split-bf16 cost and half of tf32's bytes.  Everything stored in fp16 is post-BatchNorm or post-gate, O(1..100).
 #include <math.h>
 #include <string.h>
 
@@ -25,8 +25,8 @@ namespace {
 
 struct BN { float* scale = nullptr; float* shift = nullptr; };
 
-struct ConvW {           // a 32->32 FCM convolution as a GEMM B operand [32, taps * 32] (fp32 rounded to tf32)
-  float* w = nullptr;
+struct ConvW {           // a 32->32 FCM convolution as a GEMM B operand [32, blocks * 64] fp16 (two taps per K block)
+  __half* w = nullptr;
   CUtensorMap map;
   BN bn;
 };
@@ -35,18 +35,18 @@ struct ResW { ConvW c1, c2, sc; bool stride2 = false; };
 struct DenseW {
   int cin = 0;
   BN bn1, bn2;
-  float *w1 = nullptr, *wl = nullptr;
+  __half *w1 = nullptr, *wl = nullptr;
   CUtensorMap m1, ml;
   float *cw1 = nullptr, *cb1 = nullptr, *cw2 = nullptr, *cb2 = nullptr;
 };
-struct TransW { int cin = 0, cout = 0; BN bn; float* w = nullptr; CUtensorMap m; };
+struct TransW { int cin = 0, cout = 0; BN bn; __half* w = nullptr; CUtensorMap m; };
 
 struct CamPlan {
   fy_campplus_config cfg;
   float* stem_w = nullptr; BN stem_bn;
   std::vector<ResW> res;
   ConvW fcm_out;
-  float* tdnn_w = nullptr; CUtensorMap tdnn_m; BN tdnn_bn;
+  __half* tdnn_w = nullptr; CUtensorMap tdnn_m; BN tdnn_bn;
   std::vector<std::vector<DenseW>> blocks;
   std::vector<TransW> trans;
   BN out_bn;
@@ -71,16 +71,9 @@ int dev_upload(CamPlan* p, const std::vector<T>& h, T** d) {
   FY_CUDA(cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
   return FY_OK;
 }
-// GEMM B operands stay fp32 in memory, pre-rounded (nearest, ties away) to tf32's 10-bit mantissa: the tensor core
-// ignores the low 13 bits, so rounding here makes that truncation exact.
-int upload_tf32(CamPlan* p, const std::vector<float>& h, float** d) {
-  std::vector<float> b(h.size());
-  for (size_t i = 0; i < h.size(); ++i) {
-    uint32_t u;
-    memcpy(&u, &h[i], 4);
-    if ((u & 0x7f800000u) != 0x7f800000u) u = (u + 0x1000u) & 0xffffe000u;
-    memcpy(&b[i], &u, 4);
-  }
+int upload_f16(CamPlan* p, const std::vector<float>& h, __half** d) {
+  std::vector<__half> b(h.size());
+  for (size_t i = 0; i < h.size(); ++i) b[i] = __float2half_rn(h[i]);
   return dev_upload(p, b, d);
 }
 
@@ -111,18 +104,24 @@ int load_bn(const Loader& L, const std::string& pre, int C, bool affine, BN* bn)
   return FY_OK;
 }
 
-// Conv2d weight [32, 32, kf, kt] (kf = freq taps, kt = time taps) -> B [32, kf*kt*32]: tap (dt, df) occupies
-// columns [(dt_i*kf + df_i)*32, +32), i.e. exactly one tf32 K-block.
+// Conv2d weight [32, 32, kf, kt] (kf = freq taps, kt = time taps) -> B [32, blocks * 64] fp16.  Activations are
+// channels-last with 32 channels per frequency slot, so two adjacent slots are one contiguous 64-element K block:
+//   3x3: time tap j uses block 2j = [w(j, df=-1) | w(j, df=0)] and block 2j+1 = [w(j, df=+1) | 0]      (6 blocks)
+//   1x1 (the stride-2 shortcut, which reads the odd slot of each slot pair): one block [0 | w]
 int load_fcm_conv(const Loader& L, const std::string& name, int kf, int kt, const std::string& bn_name, ConvW* out) {
   GET(w, name, 32 * 32 * kf * kt);
-  std::vector<float> b((size_t)32 * kf * kt * 32, 0.f);
+  const int nblk = kf == 3 ? 2 * kt : 1;
+  std::vector<float> b((size_t)32 * nblk * 64, 0.f);
   for (int o = 0; o < 32; ++o)
     for (int c = 0; c < 32; ++c)
       for (int i = 0; i < kf; ++i)
-        for (int j = 0; j < kt; ++j)
-          b[(size_t)o * kf * kt * 32 + (j * kf + i) * 32 + c] = w->h_data[((o * 32 + c) * kf + i) * kt + j];
-  FY_TRY(upload_tf32(L.p, b, &out->w));
-  FY_TRY(make_tmap_f32(&out->map, out->w, 32, (uint64_t)kf * kt * 32, (uint64_t)kf * kt * 32, 32));
+        for (int j = 0; j < kt; ++j) {
+          const int blk = kf == 3 ? 2 * j + (i == 2 ? 1 : 0) : 0;
+          const int half = kf == 3 ? (i == 1 ? 1 : 0) : 1;
+          b[(size_t)o * nblk * 64 + blk * 64 + half * 32 + c] = w->h_data[((o * 32 + c) * kf + i) * kt + j];
+        }
+  FY_TRY(upload_f16(L.p, b, &out->w));
+  FY_TRY(make_tmap_bf16(&out->map, out->w, 32, (uint64_t)nblk * 64, (uint64_t)nblk * 64, 32));
   return load_bn(L, bn_name, 32, true, &out->bn);
 }
 
@@ -146,20 +145,21 @@ Layout make_layout(const CamPlan* p, int n_utts, int r50, int n_seg) {
   l.o_meta = take(l.meta_ints * 4);
   l.o_m42s = take(R * 41 * 4); l.o_m42 = take(R * 42 * 4);
   l.o_m22s = take(R * 21 * 4); l.o_m22 = take(R * 22 * 4); l.o_m11s = take(R * 11 * 4);
-  // FCM activations: fp32 [time row][freq slot][32 channels] = 128 bytes per slot
-  l.o_x0 = take(R * 82 * 128);
-  l.o_y40 = take(R * 42 * 128); l.o_s40 = take(R * 42 * 128); l.o_z40a = take(R * 42 * 128); l.o_z40b = take(R * 42 * 128);
-  l.o_y20 = take(R * 22 * 128); l.o_s20 = take(R * 22 * 128); l.o_z20a = take(R * 22 * 128); l.o_z20b = take(R * 22 * 128);
-  l.o_fcm = take(R * 320 * 4);
+  // FCM activations: fp16 [time row][freq slot][32 channels] = 64 bytes per slot (+64 so the overlapping two-slot
+  // view of the last slot stays inside the buffer)
+  l.o_x0 = take(R * 82 * 64 + 64);
+  l.o_y40 = take(R * 42 * 64 + 64); l.o_s40 = take(R * 42 * 64 + 64); l.o_z40a = take(R * 42 * 64 + 64); l.o_z40b = take(R * 42 * 64 + 64);
+  l.o_y20 = take(R * 22 * 64 + 64); l.o_s20 = take(R * 22 * 64 + 64); l.o_z20a = take(R * 22 * 64 + 64); l.o_z20b = take(R * 22 * 64 + 64);
+  l.o_fcm = take(R * 320 * 2);
   int c = p->cfg.init_channels;
   for (int b = 0; b < p->cfg.n_blocks; ++b) {
     const int ctot = c + p->cfg.layers[b] * p->cfg.growth;
-    l.o_cat[b] = take((size_t)r50 * ctot * 4);
+    l.o_cat[b] = take((size_t)r50 * ctot * 2);
     c = ctot / 2;
   }
-  l.o_cat[p->cfg.n_blocks] = take((size_t)r50 * c * 4);
-  l.o_hin = take((size_t)r50 * 1024 * 4);
-  l.o_hb = take((size_t)r50 * 128 * 4);
+  l.o_cat[p->cfg.n_blocks] = take((size_t)r50 * c * 2);
+  l.o_hin = take((size_t)r50 * 1024 * 2);
+  l.o_hb = take((size_t)r50 * 128 * 2);
   l.o_gate = take((size_t)n_seg * 32 * 4);
   l.o_segsum = take((size_t)n_seg * 128 * 4);
   l.o_stats = take((size_t)n_utts * 2 * c * 4);
@@ -224,8 +224,8 @@ int fy_load_campplus(fy_ctx* ctx, const fy_tensor* t, int n, const fy_campplus_c
         for (int f = 0; f < 10; ++f)
           for (int k = 0; k < 5; ++k)
             b[(size_t)o * 1600 + k * 320 + f * 32 + ch] = w->h_data[((size_t)o * 320 + ch * 10 + f) * 5 + k];
-    FY_TRY(upload_tf32(p, b, &p->tdnn_w));
-    FY_TRY(make_tmap_f32(&p->tdnn_m, p->tdnn_w, 128, 1600, 1600, 128));
+    FY_TRY(upload_f16(p, b, &p->tdnn_w));
+    FY_TRY(make_tmap_bf16(&p->tdnn_m, p->tdnn_w, 128, 1600, 1600, 128));
     FY_TRY(load_bn(L, "tdnn_nl.0", 128, true, &p->tdnn_bn));
   }
   int ch = cfg->init_channels;
@@ -240,15 +240,15 @@ int fy_load_campplus(fy_ctx* ctx, const fy_tensor* t, int n, const fy_campplus_c
       FY_TRY(load_bn(L, pre + ".nl1.0", d.cin, true, &d.bn1));
       FY_TRY(load_bn(L, pre + ".nl2.0", 128, true, &d.bn2));
       GET(w1, pre + ".lin1.weight", 128 * d.cin);
-      FY_TRY(upload_tf32(p, std::vector<float>(w1->h_data, w1->h_data + 128 * d.cin), &d.w1));
-      FY_TRY(make_tmap_f32(&d.m1, d.w1, 128, d.cin, d.cin, 128));
+      FY_TRY(upload_f16(p, std::vector<float>(w1->h_data, w1->h_data + 128 * d.cin), &d.w1));
+      FY_TRY(make_tmap_bf16(&d.m1, d.w1, 128, d.cin, d.cin, 128));
       GET(wl, pre + ".cam.local.weight", 32 * 128 * 3);
       std::vector<float> bl((size_t)32 * 384);
       for (int o = 0; o < 32; ++o)
         for (int cc = 0; cc < 128; ++cc)
           for (int k = 0; k < 3; ++k) bl[(size_t)o * 384 + k * 128 + cc] = wl->h_data[(o * 128 + cc) * 3 + k];
-      FY_TRY(upload_tf32(p, bl, &d.wl));
-      FY_TRY(make_tmap_f32(&d.ml, d.wl, 32, 384, 384, 32));
+      FY_TRY(upload_f16(p, bl, &d.wl));
+      FY_TRY(make_tmap_bf16(&d.ml, d.wl, 32, 384, 384, 32));
       GET(a1, pre + ".cam.lin1.weight", 64 * 128); GET(a1b, pre + ".cam.lin1.bias", 64);
       GET(a2, pre + ".cam.lin2.weight", 32 * 64); GET(a2b, pre + ".cam.lin2.bias", 32);
       std::vector<float> t1((size_t)128 * 64), t2((size_t)64 * 32);  // transposed to (in, out) for coalesced reads
@@ -266,8 +266,8 @@ int fy_load_campplus(fy_ctx* ctx, const fy_tensor* t, int n, const fy_campplus_c
     const std::string pre = "transits." + std::to_string(b);
     FY_TRY(load_bn(L, pre + ".nl.0", tr.cin, true, &tr.bn));
     GET(w, pre + ".lin.weight", (int64_t)tr.cout * tr.cin);
-    FY_TRY(upload_tf32(p, std::vector<float>(w->h_data, w->h_data + (size_t)tr.cout * tr.cin), &tr.w));
-    FY_TRY(make_tmap_f32(&tr.m, tr.w, tr.cout, tr.cin, tr.cin, gemm_block_n(tr.cout)));
+    FY_TRY(upload_f16(p, std::vector<float>(w->h_data, w->h_data + (size_t)tr.cout * tr.cin), &tr.w));
+    FY_TRY(make_tmap_bf16(&tr.m, tr.w, tr.cout, tr.cin, tr.cin, gemm_block_n(tr.cout)));
     ch = tr.cout;
   }
   FY_CHECK(ch <= 512, FY_ERR_ARG, "fy_load_campplus: final width %d > 512", ch);
@@ -296,44 +296,43 @@ namespace {
 
 // one FCM 3x3 / 1x1 convolution launch
 struct FcmConv {
-  const ConvW* w; const float* in; int in_fp;            // input buffer [R100, in_fp, 32]
+  const ConvW* w; const __half* in; int in_fp;          // input buffer [R100, in_fp, 32]
   bool stride2; bool k3;                                // stride 2 in frequency; 3x3 (else 1x1)
-  float* out; int out_fp; int out_add;                  // output [R100, out_fp, 32], first valid slot
-  const int* mask; const float* resid; bool relu;
+  __half* out; int out_fp; int out_add;                 // output [R100, out_fp, 32], first valid slot
+  const int* mask; const __half* resid; bool relu;
 };
 
 int run_fcm_conv(Ctx* c, const FcmConv& f, int R100, double vframes) {
   GemmArgs g;
   g.N = 32;
-  g.tf32 = 1;
+  g.op = OP_F16;
   g.tmap_b = f.w->map;
   const int Q = f.stride2 ? f.in_fp / 2 : f.in_fp;  // GEMM rows per time row
   g.M = R100 * Q;
+  // A view: one row = two adjacent frequency slots (64 channels-last values).  Stride 2: rows are disjoint slot
+  // pairs (2q, 2q+1); stride 1: rows overlap (row g = slots g, g+1; row pitch 32 elements).
   if (f.stride2) {
-    FY_TRY(make_tmap_f32(&g.tmap_a, f.in, (uint64_t)R100 * Q, 64, 64, 128));
+    FY_TRY(make_tmap_bf16(&g.tmap_a, f.in, (uint64_t)R100 * Q, 64, 64, 128));
   } else {
-    FY_TRY(make_tmap_f32(&g.tmap_a, f.in, (uint64_t)R100 * Q, 32, 32, 128));
+    FY_TRY(make_tmap_bf16(&g.tmap_a, f.in, (uint64_t)R100 * Q, 64, 32, 128));
   }
   if (f.k3) {
-    for (int j = 0; j < 3; ++j)      // time tap dt = j - 1
-      for (int i = 0; i < 3; ++i) {  // freq tap df = i - 1
-        GemmSeg sg;
-        sg.b_col = (j * 3 + i) * 32;
-        sg.nkb = 1;
-        if (f.stride2) { sg.a_row_off = (j - 1) * Q + (i == 2 ? 1 : 0); sg.a_col = (i == 1) ? 32 : 0; }
-        else { sg.a_row_off = (j - 1) * Q + (i - 1); sg.a_col = 0; }
-        g.seg[g.nseg++] = sg;
-      }
+    for (int j = 0; j < 3; ++j) {    // time tap dt = j - 1
+      // stride 2: output q reads slots 2q, 2q+1 (view row q) and 2q+2 (view row q+1);
+      // stride 1: output g reads slots g-1, g (view row g-1) and g+1 (view row g+1)
+      g.seg[g.nseg++] = GemmSeg{(j - 1) * Q + (f.stride2 ? 0 : -1), 0, (2 * j) * 64, 1};
+      g.seg[g.nseg++] = GemmSeg{(j - 1) * Q + 1, 0, (2 * j + 1) * 64, 1};
+    }
   } else {
-    g.seg[g.nseg++] = GemmSeg{0, f.stride2 ? 32 : 0, 0, 1};
+    g.seg[g.nseg++] = GemmSeg{0, 0, 0, 1};
   }
-  g.epi.mode = EPI_F32_STORE;
-  g.epi.round_tf32 = 1;
+  g.epi.mode = EPI_BF16;
+  g.epi.out_f16 = 1;
   g.epi.act = f.relu ? ACT_RELU : ACT_NONE;
   g.epi.out = f.out; g.epi.ldo = 32;
   g.epi.scale = f.w->bn.scale; g.epi.bias = f.w->bn.shift;
   g.epi.row_idx = f.mask;
-  g.epi.resid_f32 = f.resid;
+  g.epi.resid = reinterpret_cast<const __nv_bfloat16*>(f.resid);
   if (f.stride2 || f.out_fp != Q) { g.epi.remap_q = Q; g.epi.remap_fp = f.out_fp; g.epi.remap_add = f.out_add; }
   const int fout = f.stride2 ? Q - 1 : Q - 2;
   return run_gemm(c, g, 2.0 * vframes * fout * 32 * (f.k3 ? 288 : 32));
@@ -394,6 +393,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   const int *d_rowsrc = d_meta + lay.m_rowsrc, *d_rowseg = d_meta + lay.m_rowseg, *d_segutt = d_meta + lay.m_segutt;
   auto I = [&](size_t off) { return reinterpret_cast<int*>(base + off); };
   auto Fp = [&](size_t off) { return reinterpret_cast<float*>(base + off); };
+  auto H = [&](size_t off) { return reinterpret_cast<__half*>(base + off); };
   int *m42s = I(lay.o_m42s), *m42 = I(lay.o_m42), *m22s = I(lay.o_m22s), *m22 = I(lay.o_m22), *m11s = I(lay.o_m11s);
   // zero the FCM activation buffers (pads and guard rows must read as zero) -- one contiguous span
   FY_CUDA(cudaMemsetAsync(base + lay.o_x0, 0, lay.o_fcm - lay.o_x0, st));
@@ -403,14 +403,14 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
       camk::pos_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_rowsrc, R100, Q, lo, hi, m);
     };
     mk(41, 0, 39, m42s); mk(42, 1, 40, m42); mk(21, 0, 19, m22s); mk(22, 1, 20, m22); mk(11, 0, 9, m11s);
-    camk::stem_kernel<<<R100, 320, 0, st>>>(feat, d_rowsrc, R100, p->stem_w, p->stem_bn.scale, p->stem_bn.shift, Fp(lay.o_x0));
+    camk::stem_kernel<<<R100, 320, 0, st>>>(feat, d_rowsrc, R100, p->stem_w, p->stem_bn.scale, p->stem_bn.shift, H(lay.o_x0));
     FY_CUDA(cudaGetLastError());
   }
   // ---- FCM residual stages
   {
-    struct Stage { const float* in; int in_fp; float *y, *s, *za, *zb; int fp; const int *ms, *m; };
-    Stage stg[2] = {{Fp(lay.o_x0), 82, Fp(lay.o_y40), Fp(lay.o_s40), Fp(lay.o_z40a), Fp(lay.o_z40b), 42, m42s, m42},
-                    {Fp(lay.o_z40b), 42, Fp(lay.o_y20), Fp(lay.o_s20), Fp(lay.o_z20a), Fp(lay.o_z20b), 22, m22s, m22}};
+    struct Stage { const __half* in; int in_fp; __half *y, *s, *za, *zb; int fp; const int *ms, *m; };
+    Stage stg[2] = {{H(lay.o_x0), 82, H(lay.o_y40), H(lay.o_s40), H(lay.o_z40a), H(lay.o_z40b), 42, m42s, m42},
+                    {H(lay.o_z40b), 42, H(lay.o_y20), H(lay.o_s20), H(lay.o_z20a), H(lay.o_z20b), 22, m22s, m22}};
     for (int s = 0; s < 2; ++s) {
       const Stage& S = stg[s];
       const ResW& r0 = p->res[2 * s];
@@ -421,7 +421,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
       FY_TRY(run_fcm_conv(c, FcmConv{&r1.c1, S.za, S.fp, false, true, S.y, S.fp, 0, S.m, nullptr, true}, R100, vT));
       FY_TRY(run_fcm_conv(c, FcmConv{&r1.c2, S.y, S.fp, false, true, S.zb, S.fp, 0, S.m, S.za, true}, R100, vT));
     }
-    FY_TRY(run_fcm_conv(c, FcmConv{&p->fcm_out, Fp(lay.o_z20b), 22, true, true, Fp(lay.o_fcm), 10, 0, m11s, nullptr, true}, R100, vT));
+    FY_TRY(run_fcm_conv(c, FcmConv{&p->fcm_out, H(lay.o_z20b), 22, true, true, H(lay.o_fcm), 10, 0, m11s, nullptr, true}, R100, vT));
   }
   // ---- TDNN: Conv1d(320 -> 128, k5, stride 2, pad 2) + BN + ReLU -> concat block 0, columns [0, 128)
   int ctot[4];
@@ -432,39 +432,39 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   }
   {
     GemmArgs g;
-    FY_TRY(make_tmap_f32(&g.tmap_a, Fp(lay.o_fcm), R100 / 2, 640, 640, 128));
+    FY_TRY(make_tmap_bf16(&g.tmap_a, H(lay.o_fcm), R100 / 2, 640, 640, 128));
     g.tmap_b = p->tdnn_m;
-    g.M = R50; g.N = 128; g.tf32 = 1;
-    g.seg[g.nseg++] = GemmSeg{0, 0, 0, 20};      // K blocks are 32 elements in tf32 mode
-    g.seg[g.nseg++] = GemmSeg{1, 0, 640, 20};
-    g.seg[g.nseg++] = GemmSeg{2, 0, 1280, 10};
-    g.epi.mode = EPI_F32_STORE; g.epi.act = ACT_RELU; g.epi.out = Fp(lay.o_cat[0]); g.epi.ldo = ctot[0];
+    g.M = R50; g.N = 128; g.op = OP_F16;
+    g.seg[g.nseg++] = GemmSeg{0, 0, 0, 10};
+    g.seg[g.nseg++] = GemmSeg{1, 0, 640, 10};
+    g.seg[g.nseg++] = GemmSeg{2, 0, 1280, 5};
+    g.epi.mode = EPI_BF16; g.epi.out_f16 = 1; g.epi.act = ACT_RELU; g.epi.out = H(lay.o_cat[0]); g.epi.ldo = ctot[0];
     g.epi.scale = p->tdnn_bn.scale; g.epi.bias = p->tdnn_bn.shift; g.epi.row_idx = d_rowseg;
     FY_TRY(run_gemm(c, g, 2.0 * vT2 * 128 * 1600));
   }
   // ---- dense blocks
-  float* hin = Fp(lay.o_hin);
-  float* hb = Fp(lay.o_hb);
+  __half* hin = H(lay.o_hin);
+  __half* hb = H(lay.o_hb);
   float* gate = Fp(lay.o_gate);
   float* segsum = Fp(lay.o_segsum);
   CUtensorMap m_hb;
-  FY_TRY(make_tmap_f32(&m_hb, hb, R50, 128, 128, 128));
+  FY_TRY(make_tmap_bf16(&m_hb, hb, R50, 128, 128, 128));
   for (int b = 0; b < cf.n_blocks; ++b) {
-    float* cat = Fp(lay.o_cat[b]);
+    __half* cat = H(lay.o_cat[b]);
     const int ld = ctot[b];
     const int dil = cf.dilation[b];
     for (int l = 0; l < cf.layers[b]; ++l) {
       const DenseW& d = p->blocks[b][l];
       {
-        const size_t n = (size_t)R50 * (d.cin / 4);
+        const size_t n = (size_t)R50 * (d.cin / 8);
         camk::bnrelu_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(cat, ld, R50, d.cin, d.bn1.scale, d.bn1.shift, hin, 1024);
       }
       {
         GemmArgs g;
-        FY_TRY(make_tmap_f32(&g.tmap_a, hin, R50, d.cin, 1024, 128));
-        g.tmap_b = d.m1; g.M = R50; g.N = 128; g.tf32 = 1;
-        g.seg[g.nseg++] = GemmSeg{0, 0, 0, d.cin / 32};
-        g.epi.mode = EPI_F32_STORE; g.epi.round_tf32 = 1; g.epi.act = ACT_RELU; g.epi.out = hb; g.epi.ldo = 128;
+        FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, d.cin, 1024, 128));
+        g.tmap_b = d.m1; g.M = R50; g.N = 128; g.op = OP_F16;
+        g.seg[g.nseg++] = GemmSeg{0, 0, 0, (d.cin + 63) / 64};
+        g.epi.mode = EPI_BF16; g.epi.out_f16 = 1; g.epi.act = ACT_RELU; g.epi.out = hb; g.epi.ldo = 128;
         g.epi.scale = d.bn2.scale; g.epi.bias = d.bn2.shift; g.epi.row_idx = d_rowseg;
         FY_TRY(run_gemm(c, g, 2.0 * vT2 * 128 * d.cin));
       }
@@ -473,22 +473,22 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
       camk::cam_gate_kernel<<<nseg, 128, 0, st>>>(segsum, d_T2, d_segbase, d_segutt, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
       {
         GemmArgs g;
-        g.tmap_a = m_hb; g.tmap_b = d.ml; g.M = R50; g.N = 32; g.tf32 = 1;
-        for (int k = 0; k < 3; ++k) g.seg[g.nseg++] = GemmSeg{(k - 1) * dil, 0, k * 128, 4};
-        g.epi.mode = EPI_F32_STORE; g.epi.out = cat; g.epi.ldo = ld; g.epi.col_off = d.cin;
+        g.tmap_a = m_hb; g.tmap_b = d.ml; g.M = R50; g.N = 32; g.op = OP_F16;
+        for (int k = 0; k < 3; ++k) g.seg[g.nseg++] = GemmSeg{(k - 1) * dil, 0, k * 128, 2};
+        g.epi.mode = EPI_BF16; g.epi.out_f16 = 1; g.epi.out = cat; g.epi.ldo = ld; g.epi.col_off = d.cin;
         g.epi.row_idx = d_rowseg; g.epi.row_gate = gate;
         FY_TRY(run_gemm(c, g, 2.0 * vT2 * 32 * 384));
       }
     }
     const TransW& tr = p->trans[b];
     {
-      const size_t n = (size_t)R50 * (tr.cin / 4);
+      const size_t n = (size_t)R50 * (tr.cin / 8);
       camk::bnrelu_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(cat, ld, R50, tr.cin, tr.bn.scale, tr.bn.shift, hin, 1024);
       GemmArgs g;
-      FY_TRY(make_tmap_f32(&g.tmap_a, hin, R50, tr.cin, 1024, 128));
-      g.tmap_b = tr.m; g.M = R50; g.N = tr.cout; g.tf32 = 1;
-      g.seg[g.nseg++] = GemmSeg{0, 0, 0, tr.cin / 32};
-      g.epi.mode = EPI_F32_STORE; g.epi.out = Fp(lay.o_cat[b + 1]); g.epi.ldo = ctot[b + 1];
+      FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, tr.cin, 1024, 128));
+      g.tmap_b = tr.m; g.M = R50; g.N = tr.cout; g.op = OP_F16;
+      g.seg[g.nseg++] = GemmSeg{0, 0, 0, (tr.cin + 63) / 64};
+      g.epi.mode = EPI_BF16; g.epi.out_f16 = 1; g.epi.out = H(lay.o_cat[b + 1]); g.epi.ldo = ctot[b + 1];
       g.epi.row_idx = d_rowseg;
       FY_TRY(run_gemm(c, g, 2.0 * vT2 * tr.cout * tr.cin));
     }
@@ -497,7 +497,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   const int C = ctot[cf.n_blocks];
   float* stats = Fp(lay.o_stats);
   c->launches += 12;  // memset, 5 masks, stem, 3 transit bnrelu, stats, dense
-  camk::stats_kernel<<<n_utts, 512, 0, st>>>(Fp(lay.o_cat[cf.n_blocks]), C, C, d_B, d_T2, p->out_bn.scale, p->out_bn.shift, stats);
+  camk::stats_kernel<<<n_utts, 512, 0, st>>>(H(lay.o_cat[cf.n_blocks]), C, C, d_B, d_T2, p->out_bn.scale, p->out_bn.shift, stats);
   camk::dense_kernel<<<n_utts, 256, 2 * C * 4, st>>>(stats, 2 * C, cf.embed_dim, p->dense_w, p->dense_bn.scale,
                                                      p->dense_bn.shift, emb);
   FY_CUDA(cudaGetLastError());

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -49,6 +50,8 @@ struct GemmSeg {
 // bias, rotary embedding (rotate-half inside each 64-wide head) and the d^-1/4 scale, v gets bias only; all three are
 // written as bf16 hi | lo operands for the attention / FSMN kernels (out = q, out2 = k, out3 = v).
 enum EpiMode { EPI_BF16 = 0, EPI_F32_ADD = 1, EPI_F32_STORE = 2, EPI_QKV_ROPE = 3 };
+// Operand types: bf16 and fp16 use 64-element K blocks (kind::f16), tf32 reads fp32 data in 32-element K blocks.
+enum GemmOp { OP_BF16 = 0, OP_TF32 = 1, OP_F16 = 2 };
 enum EpiAct { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2 };
 
 struct GemmEpi {
@@ -63,6 +66,7 @@ struct GemmEpi {
   const int* row_idx = nullptr;    // [M] or null: row_idx == -1 -> row written as zero; -2 -> row not written
   const float* row_gate = nullptr; // [*, N] or null: multiply by row_gate[row_idx[row] * N + n] (CAM mask)
   const __nv_bfloat16* resid = nullptr;  // EPI_BF16 only: bf16 tensor (same rows / ldo / col_off as out) added before act
+  int out_f16 = 0;                       // EPI_BF16 only: out (and resid) hold IEEE fp16 instead of bf16
   const float* resid_f32 = nullptr;      // fp32 modes: fp32 tensor (same rows / ldo / col_off as out) added before act
   int round_tf32 = 0;                    // fp32 modes: round the stored value to tf32 (operand of a later tf32 GEMM)
   // EPI_QKV_ROPE only
@@ -81,7 +85,7 @@ struct GemmArgs {
   CUtensorMap tmap_a;
   CUtensorMap tmap_b;
   int M = 0, N = 0;
-  int tf32 = 0;  // 0: bf16 operands, K blocks of 64 elements; 1: fp32 operands used as tf32, K blocks of 32 elements
+  int op = 0;    // GemmOp: operand type of A and B
   int nseg = 0;
   GemmSeg seg[kMaxSeg];
   GemmEpi epi;

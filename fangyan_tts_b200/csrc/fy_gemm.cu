@@ -29,6 +29,11 @@ template <int BN> constexpr int cta_threads() { return 128 + 32 * epi_warps<BN>(
 
 // BN = 256 (the S3 encoder's big GEMMs) owns the SM; the narrow tiles of CAMPPlus (BN = 128 / 32) have short K loops
 // and latency-bound epilogues, so two CTAs share an SM and overlap each other's epilogue with their main loops.
+__device__ __forceinline__ uint32_t pack_f16(float a, float b) {
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
 template <int BN>
 struct Cfg {
   static constexpr int kCtasPerSm = BN == 256 ? 1 : 2;
@@ -62,11 +67,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-// TF32 = false: bf16 operands, 64-element K blocks.  TF32 = true: fp32 data consumed as tf32, 32-element K blocks
-// (both are 128-byte rows, so tiles, swizzle and descriptors are identical).
-template <int BN, bool TF32>
+// OP = OP_BF16 / OP_F16: 2-byte operands, 64-element K blocks (kind::f16).  OP = OP_TF32: fp32 data consumed as tf32,
+// 32-element K blocks (kind::tf32).  All are 128-byte rows, so tiles, swizzle and descriptors are identical.
+template <int BN, int OP>
 __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_kernel(const __grid_constant__ GemmArgs args) {
   using C = Cfg<BN>;
+  constexpr bool TF32 = OP == OP_TF32;
   constexpr int BKE = TF32 ? 32 : 64;  // K elements per block
   constexpr int kEpiThreads = 32 * epi_warps<BN>();
   extern __shared__ uint8_t smem_raw[];
@@ -133,7 +139,8 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = TF32 ? ptx::make_idesc_tf32(BM, BN) : ptx::make_idesc_bf16(BM, BN);
+      constexpr uint32_t idesc = TF32 ? ptx::make_idesc_tf32(BM, BN)
+                                      : (OP == OP_F16 ? ptx::make_idesc_f16(BM, BN) : ptx::make_idesc_bf16(BM, BN));
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -290,8 +297,14 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
               const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                rs[8 * j + 2 * k] = __uint_as_float(ww[k] << 16);
-                rs[8 * j + 2 * k + 1] = __uint_as_float(ww[k] & 0xffff0000u);
+                if (e.out_f16) {
+                  const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&ww[k]));
+                  rs[8 * j + 2 * k] = f.x;
+                  rs[8 * j + 2 * k + 1] = f.y;
+                } else {
+                  rs[8 * j + 2 * k] = __uint_as_float(ww[k] << 16);
+                  rs[8 * j + 2 * k + 1] = __uint_as_float(ww[k] & 0xffff0000u);
+                }
               }
             }
           }
@@ -329,10 +342,17 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint4 w;
-              w.x = pack_bf16(x[8 * j], x[8 * j + 1]);
-              w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
-              w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]);
-              w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+              if (e.out_f16) {
+                w.x = pack_f16(x[8 * j], x[8 * j + 1]);
+                w.y = pack_f16(x[8 * j + 2], x[8 * j + 3]);
+                w.z = pack_f16(x[8 * j + 4], x[8 * j + 5]);
+                w.w = pack_f16(x[8 * j + 6], x[8 * j + 7]);
+              } else {
+                w.x = pack_bf16(x[8 * j], x[8 * j + 1]);
+                w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
+                w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]);
+                w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+              }
               dst[j] = w;
             }
             if (e.lo_col_off >= 0) {
@@ -399,18 +419,18 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
-template <int BN, bool TF32>
+template <int BN, int OP>
 int launch_bn(const GemmArgs& a, int num_sms, cudaStream_t st) {
   using C = Cfg<BN>;
   static bool configured = false;
   if (!configured) {
-    FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     configured = true;
   }
   const int tiles = ((a.M + BM - 1) / BM) * (a.N / BN);
   const int slots = num_sms * C::kCtasPerSm;
   const int grid = tiles < slots ? tiles : slots;
-  gemm_kernel<BN, TF32><<<grid, cta_threads<BN>(), C::kSmemBytes, st>>>(a);
+  gemm_kernel<BN, OP><<<grid, cta_threads<BN>(), C::kSmemBytes, st>>>(a);
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }
@@ -462,9 +482,18 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st) {
   FY_CHECK(a.M > 0 && a.nseg > 0 && a.nseg <= kMaxSeg, FY_ERR_ARG, "bad GEMM shape M=%d nseg=%d", a.M, a.nseg);
   FY_CHECK(a.epi.out != nullptr && a.epi.ldo > 0, FY_ERR_ARG, "GEMM epilogue has no output");
   switch (gemm_block_n(a.N)) {
-    case 256: return a.tf32 ? launch_bn<256, true>(a, num_sms, st) : launch_bn<256, false>(a, num_sms, st);
-    case 128: return a.tf32 ? launch_bn<128, true>(a, num_sms, st) : launch_bn<128, false>(a, num_sms, st);
-    case 32: return a.tf32 ? launch_bn<32, true>(a, num_sms, st) : launch_bn<32, false>(a, num_sms, st);
+#define FY_DISPATCH_OP(BN_)                                                          \
+  switch (a.op) {                                                                    \
+    case OP_BF16: return launch_bn<BN_, OP_BF16>(a, num_sms, st);                    \
+    case OP_TF32: return launch_bn<BN_, OP_TF32>(a, num_sms, st);                    \
+    case OP_F16: return launch_bn<BN_, OP_F16>(a, num_sms, st);                      \
+    default: FY_CHECK(false, FY_ERR_ARG, "bad GEMM operand type %d", a.op);          \
+  }                                                                                  \
+  break
+    case 256: FY_DISPATCH_OP(256);
+    case 128: FY_DISPATCH_OP(128);
+    case 32: FY_DISPATCH_OP(32);
+#undef FY_DISPATCH_OP
     default: FY_CHECK(false, FY_ERR_ARG, "GEMM N=%d must be a multiple of 32", a.N);
   }
   return FY_OK;

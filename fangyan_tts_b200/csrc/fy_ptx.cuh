@@ -151,6 +151,10 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(uint32_t m, uint32_t n) {
          | ((m >> 4) << 24);  // M / 16
 }
 
+// Same instruction with IEEE fp16 A/B (format 0).
+__host__ __device__ constexpr uint32_t make_idesc_f16(uint32_t m, uint32_t n) {
+  return (1u << 4) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
 // Instruction descriptor for kind::tf32 (A/B format 2 = TF32, both K-major), fp32 D.
 __host__ __device__ constexpr uint32_t make_idesc_tf32(uint32_t m, uint32_t n) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
