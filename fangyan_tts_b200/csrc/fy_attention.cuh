@@ -132,22 +132,31 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
     float s[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
+    // Four key blocks (independent accumulators) are interleaved so back-to-back mma.sync never wait on each other.
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int half = 0; half < 2; ++half) {
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int row = j * 8 + (lane & 7);
-        const int ch = half * 4 + (lane >> 3);
-        uint32_t b[NP][4];
+      for (int jg = 0; jg < 2; ++jg) {
+        uint32_t b[4][NP][4];
 #pragma unroll
-        for (int p = 0; p < NP; ++p) ldsm_x4(tile_addr(sK + p * TILE, row, ch), b[p][0], b[p][1], b[p][2], b[p][3]);
+        for (int jj = 0; jj < 4; ++jj) {
+          const int row = (jg * 4 + jj) * 8 + (lane & 7);
+          const int ch = half * 4 + (lane >> 3);
+#pragma unroll
+          for (int p = 0; p < NP; ++p)
+            ldsm_x4(tile_addr(sK + p * TILE, row, ch), b[jj][p][0], b[jj][p][1], b[jj][p][2], b[jj][p][3]);
+        }
 #pragma unroll
         for (int kk = 0; kk < 2; ++kk) {
           const int ks = half * 2 + kk;
-          mma16816(s[j], qf[0][ks], b[0][2 * kk], b[0][2 * kk + 1]);
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) mma16816(s[jg * 4 + jj], qf[0][ks], b[jj][0][2 * kk], b[jj][0][2 * kk + 1]);
           if (SPLIT) {
-            mma16816(s[j], qf[0][ks], b[NP - 1][2 * kk], b[NP - 1][2 * kk + 1]);
-            mma16816(s[j], qf[NP - 1][ks], b[0][2 * kk], b[0][2 * kk + 1]);
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj)
+              mma16816(s[jg * 4 + jj], qf[0][ks], b[jj][NP - 1][2 * kk], b[jj][NP - 1][2 * kk + 1]);
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) mma16816(s[jg * 4 + jj], qf[NP - 1][ks], b[jj][0][2 * kk], b[jj][0][2 * kk + 1]);
           }
         }
       }
@@ -207,19 +216,31 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
         pa[NP - 1][3] = pack2(s[2 * ks + 1][2] - bf_round(s[2 * ks + 1][2]), s[2 * ks + 1][3] - bf_round(s[2 * ks + 1][3]));
       }
 #pragma unroll
-      for (int jp = 0; jp < 4; ++jp) {  // pairs of 8-wide d tiles
-        const int row = ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-        const int ch = jp * 2 + (lane >> 4);
-        uint32_t b[NP][4];
+      for (int jpg = 0; jpg < 2; ++jpg) {  // two pairs of 8-wide d tiles = four independent accumulators
+        uint32_t b[2][NP][4];
 #pragma unroll
-        for (int p = 0; p < NP; ++p) ldsm_x4_t(tile_addr(sV + p * TILE, row, ch), b[p][0], b[p][1], b[p][2], b[p][3]);
+        for (int jj = 0; jj < 2; ++jj) {
+          const int row = ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+          const int ch = (jpg * 2 + jj) * 2 + (lane >> 4);
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          mma16816(o[jp * 2 + t], pa[0], b[0][2 * t], b[0][2 * t + 1]);
-          if (SPLIT) {
-            mma16816(o[jp * 2 + t], pa[NP - 1], b[0][2 * t], b[0][2 * t + 1]);
-            mma16816(o[jp * 2 + t], pa[0], b[NP - 1][2 * t], b[NP - 1][2 * t + 1]);
-          }
+          for (int p = 0; p < NP; ++p)
+            ldsm_x4_t(tile_addr(sV + p * TILE, row, ch), b[jj][p][0], b[jj][p][1], b[jj][p][2], b[jj][p][3]);
+        }
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+          for (int t = 0; t < 2; ++t) mma16816(o[(jpg * 2 + jj) * 2 + t], pa[0], b[jj][0][2 * t], b[jj][0][2 * t + 1]);
+        if (SPLIT) {
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+              mma16816(o[(jpg * 2 + jj) * 2 + t], pa[NP - 1], b[jj][0][2 * t], b[jj][0][2 * t + 1]);
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj)
+#pragma unroll
+            for (int t = 0; t < 2; ++t)
+              mma16816(o[(jpg * 2 + jj) * 2 + t], pa[0], b[jj][NP - 1][2 * t], b[jj][NP - 1][2 * t + 1]);
         }
       }
     }
