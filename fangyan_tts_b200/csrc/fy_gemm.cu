@@ -11,6 +11,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "fy_common.cuh"
 #include "fy_ptx.cuh"
@@ -27,19 +28,22 @@ constexpr int BK = 64;
 template <int BN> constexpr int epi_warps() { return BN == 256 ? 8 : 4; }
 template <int BN> constexpr int cta_threads() { return 128 + 32 * epi_warps<BN>(); }
 
-// BN = 256 (the S3 encoder's big GEMMs) owns the SM; the narrow tiles of CAMPPlus (BN = 128 / 32) have short K loops
-// and latency-bound epilogues, so two CTAs share an SM and overlap each other's epilogue with their main loops.
 __device__ __forceinline__ uint32_t pack_f16(float a, float b) {
   __half2 v = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int BN>
+// BN = 256 (the S3 encoder's big GEMMs) owns the SM; the narrow tiles of CAMPPlus (BN = 128 / 32) have short K loops
+// and latency-bound epilogues, so two CTAs share an SM and overlap each other's epilogue with their main loops.
+// NCTA = 2 is the CTA-pair form of the BN = 256 kernel: two SMs of one cluster compute a 256 x 256 tile with
+// tcgen05.mma.cta_group::2, each holding 128 rows of A and HALF of the B tile, which cuts the B traffic from L2 and
+// the shared-memory reads per MMA by a third and frees room for a 6-deep ring.
+template <int BN, int NCTA = 1>
 struct Cfg {
   static constexpr int kCtasPerSm = BN == 256 ? 1 : 2;
-  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 3 : 4);
+  static constexpr int kStages = NCTA == 2 ? 6 : (BN == 256 ? 4 : (BN == 128 ? 3 : 4));
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBBytes = BN / NCTA * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kAccStages = BN == 32 ? 4 : 2;   // TMEM accumulator ring
   static constexpr int kTmemCols = kAccStages * BN < 32 ? 32 : kAccStages * BN;
@@ -69,9 +73,13 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 
 // OP = OP_BF16 / OP_F16: 2-byte operands, 64-element K blocks (kind::f16).  OP = OP_TF32: fp32 data consumed as tf32,
 // 32-element K blocks (kind::tf32).  All are 128-byte rows, so tiles, swizzle and descriptors are identical.
-template <int BN, int OP>
-__global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_kernel(const __grid_constant__ GemmArgs args) {
-  using C = Cfg<BN>;
+template <int BN, int OP, int NCTA>
+__global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) gemm_kernel(const __grid_constant__ GemmArgs args) {
+  using C = Cfg<BN, NCTA>;
+  constexpr bool PAIR = NCTA == 2;
+  const uint32_t cta_rank = PAIR ? ptx::cluster_ctarank() : 0u;   // rank 0 = the pair's leader (issues the MMAs)
+  const int worker = PAIR ? blockIdx.x >> 1 : blockIdx.x;         // persistent tile worker = CTA or CTA pair
+  const int n_workers = PAIR ? gridDim.x >> 1 : gridDim.x;
   constexpr bool TF32 = OP == OP_TF32;
   constexpr int BKE = TF32 ? 32 : 64;  // K elements per block
   constexpr int kEpiThreads = 32 * epi_warps<BN>();
@@ -89,7 +97,8 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  const int num_m = (args.M + BM - 1) / BM;
+  constexpr int TM = BM * NCTA;                                  // rows per tile (per pair)
+  const int num_m = (args.M + TM - 1) / TM;
   const int num_n = args.N / BN;
   const int num_tiles = num_m * num_n;
 
@@ -98,19 +107,25 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
     ptx::prefetch_tmap(&args.tmap_b);
   }
   if (warp == 1 && lane == 0) {
+    // pair: the leader's full barrier collects both producers' arrivals and both CTAs' TMA bytes; its tempty
+    // barrier collects both CTAs' epilogue threads.  empty / tfull are signalled in both CTAs by multicast commits.
     for (int i = 0; i < C::kStages; ++i) {
-      ptx::mbar_init(&full_bar[i], 1);
+      ptx::mbar_init(&full_bar[i], NCTA);
       ptx::mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < C::kAccStages; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
-      ptx::mbar_init(&tempty_bar[i], kEpiThreads);
+      ptx::mbar_init(&tempty_bar[i], kEpiThreads * NCTA);
     }
     ptx::fence_mbar_init();
   }
-  if (warp == 2) ptx::tmem_alloc<C::kTmemCols>(tmem_holder);
+  if (PAIR) ptx::cluster_sync();   // both CTAs are resident before TMEM is allocated pair-wide
+  if (warp == 2) {
+    if (PAIR) ptx::tmem_alloc_pair<C::kTmemCols>(tmem_holder);
+    else ptx::tmem_alloc<C::kTmemCols>(tmem_holder);
+  }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (PAIR) ptx::cluster_sync(); else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
@@ -119,18 +134,25 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / num_n) * BM;
-        const int n0 = (tile % num_n) * BN;
+      for (int tile = worker; tile < num_tiles; tile += n_workers) {
+        const int m0 = (tile / num_n) * TM + (int)cta_rank * BM;
+        const int n0 = (tile % num_n) * BN + (int)cta_rank * (BN / NCTA);   // pair: this CTA's half of the B tile
         for (int s = 0; s < args.nseg; ++s) {
           const GemmSeg sg = args.seg[s];
           for (int kb = 0; kb < sg.nkb; ++kb) {
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* a_dst = tiles + stage * C::kStageBytes;
             uint8_t* b_dst = a_dst + C::kABytes;
-            ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes);
-            ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
-            ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
+            if (PAIR) {
+              if (cta_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes * 2);
+              else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
+              ptx::tma_load_2d_pair(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
+              ptx::tma_load_2d_pair(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
+            } else {
+              ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes);
+              ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
+              ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
+            }
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -138,14 +160,14 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = TF32 ? ptx::make_idesc_tf32(BM, BN)
-                                      : (OP == OP_F16 ? ptx::make_idesc_f16(BM, BN) : ptx::make_idesc_bf16(BM, BN));
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = TF32 ? ptx::make_idesc_tf32(TM, BN)
+                                      : (OP == OP_F16 ? ptx::make_idesc_f16(TM, BN) : ptx::make_idesc_bf16(TM, BN));
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = worker; tile < num_tiles; tile += n_workers) {
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
@@ -160,15 +182,18 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
             const uint64_t db = ptx::make_desc_sw128(a_addr + C::kABytes);
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
-              if (TF32) ptx::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              if (PAIR) ptx::mma_bf16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              else if (TF32) ptx::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
               else ptx::mma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
               accumulate = 1;
             }
-            ptx::mma_commit(&empty_bar[stage]);
+            if (PAIR) ptx::mma_commit_pair(&empty_bar[stage]);
+            else ptx::mma_commit(&empty_bar[stage]);
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
           }
         }
-        ptx::mma_commit(&tfull_bar[as]);
+        if (PAIR) ptx::mma_commit_pair(&tfull_bar[as]);
+        else ptx::mma_commit(&tfull_bar[as]);
         if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
       }
     }
@@ -182,8 +207,8 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
     int as = 0;
     uint32_t aphase = 0;
     int staged_n0 = -1;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile / num_n) * BM;
+    for (int tile = worker; tile < num_tiles; tile += n_workers) {
+      const int m0 = (tile / num_n) * TM + (int)cta_rank * BM;
       const int n0 = (tile % num_n) * BN;
       if (n0 != staged_n0) {  // per-column scale / bias of this N block -> shared memory (uniform branch)
         asm volatile("bar.sync 1, %0;\n" ::"n"(kEpiThreads) : "memory");
@@ -276,7 +301,7 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
           }
         }
         ptx::tc_fence_before();
-        ptx::mbar_arrive(&tempty_bar[as]);
+        if (PAIR) ptx::mbar_arrive_cluster(&tempty_bar[as], 0); else ptx::mbar_arrive(&tempty_bar[as]);
         if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
         continue;
       }
@@ -390,16 +415,17 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN>::kCtasPerSm) gemm_k
         }
       }
       ptx::tc_fence_before();
-      ptx::mbar_arrive(&tempty_bar[as]);
+      if (PAIR) ptx::mbar_arrive_cluster(&tempty_bar[as], 0); else ptx::mbar_arrive(&tempty_bar[as]);
       if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
     }
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if (PAIR) ptx::cluster_sync(); else __syncthreads();
   if (warp == 2) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc<C::kTmemCols>(tmem_base);
+    if (PAIR) ptx::tmem_dealloc_pair<C::kTmemCols>(tmem_base);
+    else ptx::tmem_dealloc<C::kTmemCols>(tmem_base);
   }
 }
 
@@ -419,20 +445,46 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
-template <int BN, int OP>
+template <int BN, int OP, int NCTA>
 int launch_bn(const GemmArgs& a, int num_sms, cudaStream_t st) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, NCTA>;
   static bool configured = false;
   if (!configured) {
-    FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, OP, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     configured = true;
   }
-  const int tiles = ((a.M + BM - 1) / BM) * (a.N / BN);
-  const int slots = num_sms * C::kCtasPerSm;
-  const int grid = tiles < slots ? tiles : slots;
-  gemm_kernel<BN, OP><<<grid, cta_threads<BN>(), C::kSmemBytes, st>>>(a);
+  const int tiles = ((a.M + BM * NCTA - 1) / (BM * NCTA)) * (a.N / BN);
+  const int slots = num_sms * C::kCtasPerSm / NCTA;
+  const int workers = tiles < slots ? tiles : slots;
+  if (NCTA == 1) {
+    gemm_kernel<BN, OP, NCTA><<<workers, cta_threads<BN>(), C::kSmemBytes, st>>>(a);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(workers * NCTA);
+    cfg.blockDim = dim3(cta_threads<BN>());
+    cfg.dynamicSmemBytes = C::kSmemBytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = NCTA;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    FY_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, OP, NCTA>, a));
+  }
   FY_CUDA(cudaGetLastError());
   return FY_OK;
+}
+
+// CTA pairs pay off once there are enough 256-row tiles to keep all pairs busy; FY_GEMM_2CTA=0 turns them off.
+bool use_pair(const GemmArgs& a) {
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("FY_GEMM_2CTA");
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  return enabled && a.op == OP_BF16 && a.N % 256 == 0 && a.M >= 2048;
 }
 
 }  // namespace
@@ -484,13 +536,15 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st) {
   switch (gemm_block_n(a.N)) {
 #define FY_DISPATCH_OP(BN_)                                                          \
   switch (a.op) {                                                                    \
-    case OP_BF16: return launch_bn<BN_, OP_BF16>(a, num_sms, st);                    \
-    case OP_TF32: return launch_bn<BN_, OP_TF32>(a, num_sms, st);                    \
-    case OP_F16: return launch_bn<BN_, OP_F16>(a, num_sms, st);                      \
+    case OP_BF16: return launch_bn<BN_, OP_BF16, 1>(a, num_sms, st);                 \
+    case OP_TF32: return launch_bn<BN_, OP_TF32, 1>(a, num_sms, st);                 \
+    case OP_F16: return launch_bn<BN_, OP_F16, 1>(a, num_sms, st);                   \
     default: FY_CHECK(false, FY_ERR_ARG, "bad GEMM operand type %d", a.op);          \
   }                                                                                  \
   break
-    case 256: FY_DISPATCH_OP(256);
+    case 256:
+      if (use_pair(a)) return launch_bn<256, OP_BF16, 2>(a, num_sms, st);
+      FY_DISPATCH_OP(256);
     case 128: FY_DISPATCH_OP(128);
     case 32: FY_DISPATCH_OP(32);
 #undef FY_DISPATCH_OP

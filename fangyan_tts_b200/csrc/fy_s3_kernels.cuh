@@ -121,22 +121,33 @@ __global__ void __launch_bounds__(128, 4) fsmn_kernel(const __nv_bfloat16* __res
     const int t = t0 + r0 + i;
     if (t < L) asm volatile("prefetch.global.L2 [%0];\n" ::"l"(x + (size_t)(P + t) * D + c0 + c4 * 4));
   }
-  for (int i = threadIdx.x; i < kSpan * 16; i += 128) {
+  // stage v: all global loads of this thread are issued before any is consumed (one round trip, not twelve)
+  constexpr int kIters = (kSpan * 16 + 127) / 128;
+  uint2 gh[kIters], gl[kIters];
+#pragma unroll
+  for (int it = 0; it < kIters; ++it) {
+    const int i = threadIdx.x + it * 128;
     const int rr = i >> 4, cc = i & 15;
     const int t = t0 - kPad + rr;
-    float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (t >= 0 && t < L) {
+    gh[it] = make_uint2(0u, 0u);
+    gl[it] = make_uint2(0u, 0u);
+    if (i < kSpan * 16 && t >= 0 && t < L) {
       const __nv_bfloat16* src = v + (size_t)(P + t) * ldv + c0 + cc * 4;
-      const uint2 h = __ldg(reinterpret_cast<const uint2*>(src));
-      val.x = __uint_as_float(h.x << 16); val.y = __uint_as_float(h.x & 0xffff0000u);
-      val.z = __uint_as_float(h.y << 16); val.w = __uint_as_float(h.y & 0xffff0000u);
-      if (SPLIT) {
-        const uint2 l = __ldg(reinterpret_cast<const uint2*>(src + lo_off));
-        val.x += __uint_as_float(l.x << 16); val.y += __uint_as_float(l.x & 0xffff0000u);
-        val.z += __uint_as_float(l.y << 16); val.w += __uint_as_float(l.y & 0xffff0000u);
-      }
+      gh[it] = __ldg(reinterpret_cast<const uint2*>(src));
+      if (SPLIT) gl[it] = __ldg(reinterpret_cast<const uint2*>(src + lo_off));
     }
-    sv[rr][cc] = val;
+  }
+#pragma unroll
+  for (int it = 0; it < kIters; ++it) {
+    const int i = threadIdx.x + it * 128;
+    if (i < kSpan * 16) {
+      float4 val;
+      val.x = __uint_as_float(gh[it].x << 16) + __uint_as_float(gl[it].x << 16);
+      val.y = __uint_as_float(gh[it].x & 0xffff0000u) + __uint_as_float(gl[it].x & 0xffff0000u);
+      val.z = __uint_as_float(gh[it].y << 16) + __uint_as_float(gl[it].y << 16);
+      val.w = __uint_as_float(gh[it].y & 0xffff0000u) + __uint_as_float(gl[it].y & 0xffff0000u);
+      sv[i >> 4][i & 15] = val;
+    }
   }
   for (int i = threadIdx.x; i < KS * 16; i += 128)
     sw[i >> 4][i & 15] = __ldg(reinterpret_cast<const float4*>(w + (size_t)(i >> 4) * D + c0 + (i & 15) * 4));
@@ -158,11 +169,17 @@ __global__ void __launch_bounds__(128, 4) fsmn_kernel(const __nv_bfloat16* __res
       acc[i].z = fmaf(ww.z, vv.z, acc[i].z); acc[i].w = fmaf(ww.w, vv.w, acc[i].w);
     }
   }
+  float4 xv[kFsmnPerThread];
+#pragma unroll
+  for (int i = 0; i < kFsmnPerThread; ++i) {
+    const int t = t0 + r0 + i;
+    xv[i] = t < L ? *reinterpret_cast<const float4*>(x + (size_t)(P + t) * D + c0 + c4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
 #pragma unroll
   for (int i = 0; i < kFsmnPerThread; ++i) {
     const int t = t0 + r0 + i;
     if (t < L) {
-      float4 o = *reinterpret_cast<const float4*>(x + (size_t)(P + t) * D + c0 + c4 * 4);
+      float4 o = xv[i];
       o.x += acc[i].x; o.y += acc[i].y; o.z += acc[i].z; o.w += acc[i].w;
       *reinterpret_cast<float4*>(x + (size_t)(P + t) * D + c0 + c4 * 4) = o;
     }
