@@ -107,15 +107,16 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
     ptx::prefetch_tmap(&args.tmap_b);
   }
   if (warp == 1 && lane == 0) {
-    // pair: the leader's full barrier collects both producers' arrivals and both CTAs' TMA bytes; its tempty
-    // barrier collects both CTAs' epilogue threads.  empty / tfull are signalled in both CTAs by multicast commits.
+    // pair: the leader's full barrier takes one arrival (its own producer, which posts the byte count of BOTH CTAs'
+    // loads) plus both CTAs' TMA bytes; its tempty barrier collects one arrival per epilogue warp of both CTAs.
+    // empty / tfull are signalled in both CTAs by multicast commits.
     for (int i = 0; i < C::kStages; ++i) {
-      ptx::mbar_init(&full_bar[i], NCTA);
+      ptx::mbar_init(&full_bar[i], 1);
       ptx::mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < C::kAccStages; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
-      ptx::mbar_init(&tempty_bar[i], kEpiThreads * NCTA);
+      ptx::mbar_init(&tempty_bar[i], epi_warps<BN>() * NCTA);
     }
     ptx::fence_mbar_init();
   }
@@ -144,14 +145,18 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
             uint8_t* a_dst = tiles + stage * C::kStageBytes;
             uint8_t* b_dst = a_dst + C::kABytes;
             if (PAIR) {
+              // The peer's bytes may land on the leader's barrier before this expect_tx: harmless, the phase cannot
+              // complete until this (the only) arrival, and the peer cannot run a ring revolution ahead because its
+              // empty barrier is only released by the leader's MMA commit.
               if (cta_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes * 2);
-              else ptx::mbar_arrive_cluster(&full_bar[stage], 0);
               ptx::tma_load_2d_pair(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
               ptx::tma_load_2d_pair(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
             } else {
               ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes);
               ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
               ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
+              if (BN == 256)   // tensor-map boxes are at most 128 rows (shared with the pair kernel): second half
+                ptx::tma_load_2d(b_dst + 128 * 128, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0 + 128);
             }
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
           }
@@ -301,7 +306,10 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
           }
         }
         ptx::tc_fence_before();
-        if (PAIR) ptx::mbar_arrive_cluster(&tempty_bar[as], 0); else ptx::mbar_arrive(&tempty_bar[as]);
+        __syncwarp();
+        if (lane == 0) {
+          if (PAIR) ptx::mbar_arrive_cluster(&tempty_bar[as], 0); else ptx::mbar_arrive(&tempty_bar[as]);
+        }
         if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
         continue;
       }
@@ -415,7 +423,10 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
         }
       }
       ptx::tc_fence_before();
-      if (PAIR) ptx::mbar_arrive_cluster(&tempty_bar[as], 0); else ptx::mbar_arrive(&tempty_bar[as]);
+      __syncwarp();
+        if (lane == 0) {
+          if (PAIR) ptx::mbar_arrive_cluster(&tempty_bar[as], 0); else ptx::mbar_arrive(&tempty_bar[as]);
+        }
       if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
     }
   }
@@ -490,6 +501,7 @@ bool use_pair(const GemmArgs& a) {
 }  // namespace
 
 int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  if (box_rows > 128) box_rows = 128;  // 256-wide B tiles are fetched as two 128-row boxes
   EncodeTiledFn enc = get_encode();
   FY_CHECK(enc != nullptr, FY_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   FY_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 2) % 16 == 0, FY_ERR_ARG,
@@ -507,6 +519,7 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t c
 }
 
 int make_tmap_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  if (box_rows > 128) box_rows = 128;  // 256-wide B tiles are fetched as two 128-row boxes
   EncodeTiledFn enc = get_encode();
   FY_CHECK(enc != nullptr, FY_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   FY_CHECK((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * 4) % 16 == 0, FY_ERR_ARG,

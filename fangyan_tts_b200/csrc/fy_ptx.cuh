@@ -83,13 +83,15 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
 }
 
 // CTA-pair variant: the data lands in this CTA's shared memory, the byte count is signalled on the mbarrier at the
-// same offset in the pair's leader (even-ranked) CTA -- bit 24 of a shared::cluster address selects the peer.
+// same offset in the pair's leader CTA (rank 0 of the cluster), addressed through mapa.
 __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int32_t c0,
                                                  int32_t c1) {
   asm volatile(
+      "{\n\t.reg .b32 rb;\n\t"
+      "mapa.shared::cluster.u32 rb, %2, 0;\n\t"
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], "
-      "[%2];\n" ::"r"(smem_u32(smem_dst)),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      "[rb];\n\t}\n" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
 
