@@ -96,6 +96,19 @@ __device__ __forceinline__ int find_utt(const int* __restrict__ off, int n, int 
   return lo;
 }
 
+// Frame pairs never straddle utterances: utterance u owns pair slots [s(u), s(u+1)), s(u) = (frame_off[u] + u) >> 1,
+// which is always at least ceil(M_u / 2) slots.  A frame's FFT partner (the other lane of the packed complex
+// transform, whose rounding noise leaks into it at the 1e-5 level) is therefore fixed by its own utterance, and
+// every result is bit-identical whatever else is in the batch.  Returns the utterance of slot w; n = #utterances.
+__device__ __forceinline__ int find_slot_utt(const int* __restrict__ off, int n, int w) {
+  int lo = 0, hi = n;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (((__ldg(off + mid) + mid) >> 1) <= w) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
 template <bool S16>
 __device__ __forceinline__ float load_pcm(const void* pcm, int idx) {
   if (S16) return (float)__ldg(reinterpret_cast<const short*>(pcm) + idx) * (1.0f / 32768.0f);
@@ -127,20 +140,20 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fbank_kernel(const void* 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float2* A = sbuf[warp][0];
   float2* B = sbuf[warp][1];
-  const int pair = blockIdx.x * kWarpsPerBlock + warp;
-  const int gf0 = pair * 2;
-  if (gf0 >= total_frames) return;
+  const int slot = blockIdx.x * kWarpsPerBlock + warp;
+  if (slot >= ((total_frames + n_utts) >> 1)) return;
+  const int u = find_slot_utt(frame_off, n_utts, slot);
+  const int fo = __ldg(frame_off + u);
+  const int f0 = 2 * (slot - ((fo + u) >> 1));          // first frame of the pair inside utterance u
+  const int nf = __ldg(frame_off + u + 1) - fo;
+  if (f0 >= nf) return;
+  const int gf0 = fo + f0;
   int start[2];
   bool valid[2];
 #pragma unroll
   for (int f = 0; f < 2; ++f) {
-    const int gf = gf0 + f;
-    valid[f] = gf < total_frames;
-    start[f] = 0;
-    if (valid[f]) {
-      const int u = find_utt(frame_off, n_utts, gf);
-      start[f] = __ldg(pcm_off + u) + (gf - __ldg(frame_off + u)) * 160;
-    }
+    valid[f] = f0 + f < nf;
+    start[f] = __ldg(pcm_off + u) + (f0 + f) * 160;
   }
   // raw samples -> B, frame sums
   float s0 = 0.f, s1 = 0.f;
@@ -232,23 +245,23 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) logmel_kernel(const void*
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float2* A = sbuf[warp][0];
   float2* B = sbuf[warp][1];
-  const int pair = blockIdx.x * kWarpsPerBlock + warp;
-  const int gf0 = pair * 2;
-  if (gf0 >= total_frames) return;
+  const int slot = blockIdx.x * kWarpsPerBlock + warp;
+  if (slot >= ((total_frames + n_utts) >> 1)) return;
+  const int u = find_slot_utt(frame_off, n_utts, slot);
+  const int fo = __ldg(frame_off + u);
+  const int f0 = 2 * (slot - ((fo + u) >> 1));          // first frame of the pair inside utterance u
+  const int nf = __ldg(frame_off + u + 1) - fo;
+  if (f0 >= nf) return;
+  const int gf0 = fo + f0;
   int base[2], nsamp[2], center[2], utt[2];
   bool valid[2];
 #pragma unroll
   for (int f = 0; f < 2; ++f) {
-    const int gf = gf0 + f;
-    valid[f] = gf < total_frames;
-    base[f] = 0; nsamp[f] = 1; center[f] = 0; utt[f] = 0;
-    if (valid[f]) {
-      const int u = find_utt(frame_off, n_utts, gf);
-      utt[f] = u;
-      base[f] = __ldg(pcm_off + u);
-      nsamp[f] = __ldg(pcm_off + u + 1) - base[f];
-      center[f] = (gf - __ldg(frame_off + u)) * 160;
-    }
+    valid[f] = f0 + f < nf;
+    utt[f] = u;
+    base[f] = __ldg(pcm_off + u);
+    nsamp[f] = __ldg(pcm_off + u + 1) - base[f];
+    center[f] = (f0 + f) * 160;
   }
   for (int i = lane; i < 400; i += 32) {
     float2 v = make_float2(0.f, 0.f);
@@ -462,7 +475,7 @@ int launch_fbank(Ctx* c, const void* pcm, int dtype, const int* pcm_off, const i
                  int total_frames, float* feat) {
   if (total_frames <= 0) return FY_OK;
   MelTable mt{c->fb_mel_w, c->fb_mel_off, c->fb_mel_len, c->fb_mel_ptr};
-  const int pairs = (total_frames + 1) / 2;
+  const int pairs = ((total_frames + n_utts) >> 1) + 1;   // utterance-local pair slots (see find_slot_utt)
   const int grid = (pairs + kWarpsPerBlock - 1) / kWarpsPerBlock;
   if (dtype == FY_PCM_S16)
     fbank_kernel<true><<<grid, kWarpsPerBlock * 32, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,
@@ -483,7 +496,7 @@ int launch_logmel_raw(Ctx* c, const void* pcm, int dtype, const int* pcm_off, co
   if (total_frames <= 0) return FY_OK;
   MelTable mt{c->wh_mel_w, c->wh_mel_off, c->wh_mel_len, c->wh_mel_ptr};
   fill_int_kernel<<<(n_utts + 255) / 256, 256, 0, c->stream>>>(umax, n_utts, (int)0x80000000);
-  const int pairs = (total_frames + 1) / 2;
+  const int pairs = ((total_frames + n_utts) >> 1) + 1;   // utterance-local pair slots (see find_slot_utt)
   const int grid = (pairs + kWarpsPerBlock - 1) / kWarpsPerBlock;
   if (dtype == FY_PCM_S16)
     logmel_kernel<true><<<grid, kWarpsPerBlock * 32, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,

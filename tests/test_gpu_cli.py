@@ -43,7 +43,7 @@ def data_dir(tmp_path_factory):
 
 def _run(tool, d, weights, env_extra=None):
     import os
-    env = dict(os.environ, FY_GPUS="1", **(env_extra or {}))
+    env = dict(os.environ, **{"FY_GPUS": "1", **(env_extra or {})})
     r = subprocess.run([sys.executable, str(ROOT / "tools" / tool), "--dir", str(d), "--onnx_path", str(weights),
                         "--num_thread", "4"], capture_output=True, text=True, env=env)
     assert r.returncode == 0, r.stderr[-2000:]
@@ -100,6 +100,30 @@ def test_extract_speech_token_cli(data_dir):
         bad += sum(a != b for a, b in zip(u2t[k], ref))
     assert len(u2t[keys[-2]]) == 750                                             # exactly 30.0 s is tokenised
     assert bad / total <= 1e-3, (bad, total)
+
+
+def test_cli_two_gpus_matches_one(data_dir, tmp_path):
+    """Self-spawned multi-GPU run (one worker per GPU, NCCL gather) writes the same files as the single-GPU run."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import shutil
+    d, keys, utts, st = data_dir
+    for name in ("wav.scp", "utt2spk"):
+        shutil.copy(d / name, tmp_path / name)
+    _run("extract_embedding.py", tmp_path, d / "campplus.npz", {"FY_GPUS": "2"})
+    _run("extract_speech_token.py", tmp_path, d / "s3tok.npz", {"FY_GPUS": "2", "FY_S3TOK_CONFIG": str(d / "s3.json")})
+    if not (d / "utt2embedding.pt").exists():
+        _run("extract_embedding.py", d, d / "campplus.npz")
+    if not (d / "utt2speech_token.pt").exists():
+        _run("extract_speech_token.py", d, d / "s3tok.npz", {"FY_S3TOK_CONFIG": str(d / "s3.json")})
+    a, b = torch.load(d / "utt2embedding.pt"), torch.load(tmp_path / "utt2embedding.pt")
+    assert sorted(a) == sorted(b)
+    for k in a:     # batches differ between 1 and 2 ranks, results must not (each utterance is computed alone)
+        assert a[k] == b[k], k
+    assert torch.load(d / "utt2speech_token.pt") == torch.load(tmp_path / "utt2speech_token.pt")
+    sa, sb = torch.load(d / "spk2embedding.pt"), torch.load(tmp_path / "spk2embedding.pt")
+    for k in sa:
+        assert torch.allclose(torch.tensor(sa[k]), torch.tensor(sb[k]), atol=1e-5)
 
 
 def test_cli_is_all_or_nothing(data_dir, tmp_path):
