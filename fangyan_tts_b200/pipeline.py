@@ -125,6 +125,46 @@ class Extractor:
             out[idx] = emb
         return out
 
+    # ------------------------------------------------------------------ both stages, one upload
+    def extract(self, utts: Sequence[Utt]):
+        """Stages 1 and 2 over the same utterances: (embeddings float32 [n, 192], token lists) on the host, original
+        order.  16 kHz mono PCM16 input (what prepare_training_data.py writes) is uploaded once per batch as int16 and
+        feeds both front-ends; results stay on the device until the last batch has been launched, so host staging of
+        batch k+1 overlaps the kernels of batch k.  Anything else takes the two single-stage paths."""
+        fused = all(u.sr == SR and u.samples.dtype == np.int16 and u.samples.shape[1] == 1 and
+                    u.samples.shape[0] / SR <= MAX_TOKEN_SECONDS and u.samples.shape[0] >= 400 for u in utts)
+        if not fused:
+            return self.embed(utts), self.tokenize(utts)
+        dur = [u.samples.shape[0] / SR for u in utts]
+        batches = plan_batches(dur, self.max_batch_seconds, self.max_batch_utts)
+        total = sum(u.samples.shape[0] for u in utts)
+        if self._pin is None or self._pin.numel() < total:
+            self._pin = torch.empty(max(total, 1), dtype=torch.int16).pin_memory()
+        host = self._pin.numpy()
+        pending, o = [], 0
+        for idx in batches:
+            lens = [utts[i].samples.shape[0] for i in idx]
+            b0 = o
+            for i, n in zip(idx, lens):
+                host[o:o + n] = utts[i].samples[:, 0]
+                o += n
+            pcm = self._pin[b0:o].to(self.eng.device, non_blocking=True)
+            feat, frames = self.eng.fbank_cmn(pcm, lens)
+            emb = self.eng.campplus(feat, frames)
+            mel, mframes = self.eng.logmel(pcm, lens)
+            tok, counts = self.eng.s3tok(mel, mframes)
+            pending.append((idx, emb, tok, counts))
+        out = np.zeros((len(utts), 192), dtype=np.float32)
+        toks: List[List[int]] = [[] for _ in utts]
+        for idx, emb, tok, counts in pending:
+            out[idx] = emb.cpu().numpy()
+            th = tok.cpu().numpy()
+            p = 0
+            for i, n in zip(idx, counts):
+                toks[i] = th[p:p + n].tolist()
+                p += n
+        return out, toks
+
     # ------------------------------------------------------------------ stage 2
     def tokenize_batch(self, utts: Sequence[Utt]):
         """(packed int32 tokens on the device, token counts) for one batch; every utterance must pass the gate."""
