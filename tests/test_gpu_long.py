@@ -1,0 +1,54 @@
+"""BASELINE configs[3]: long-utterance stress -- clips up to the 30 s cap, a 256-utterance packed batch, parity
+against the oracle on a sample (the oracle cannot do the whole batch in seconds) and the size-independent checks
+on all of it: token counts bit-exact, ids inside the FSQ vocabulary, embeddings finite and unit-comparable."""
+import numpy as np
+import pytest
+import torch
+
+from fangyan_tts_b200 import synth, synth_weights
+from fangyan_tts_b200.configs import CamPlusConfig, S3Config
+from fangyan_tts_b200.engine import token_len
+from oracle import campplus as CP
+from oracle import frontend as F
+from oracle import s3tokenizer as S3
+
+pytestmark = pytest.mark.gpu
+
+
+def test_long_utterance_batch_256(engine):
+    cfg = S3Config(n_layer=2)
+    engine.load_campplus(synth_weights.campplus_state(seed=3), CamPlusConfig())
+    engine.load_s3tok(synth_weights.s3tok_state(cfg, seed=4), cfg)
+    rng = np.random.default_rng(1986 + 3)
+    pool = [synth.utterance(rng, 30.0) for _ in range(6)]
+    utts = []
+    for i in range(256):
+        n = 480000 if i in (0, 255) else int(rng.uniform(1.0, 30.0) * 16000)     # two clips at exactly 30.0 s
+        utts.append(np.ascontiguousarray(pool[i % 6][:n]))
+    pcm = torch.from_numpy(np.concatenate(utts)).cuda()
+    lens = [len(u) for u in utts]
+    feat, frames = engine.fbank_cmn(pcm, lens)
+    emb = engine.campplus(feat, frames).cpu()
+    mel, mframes = engine.logmel(pcm, lens)
+    tok, counts = engine.s3tok(mel, mframes)
+    tok = tok.cpu()
+    assert counts == [token_len(n // 160) for n in lens] and counts[0] == 750
+    assert int(tok.min()) >= 0 and int(tok.max()) < 6561
+    assert torch.isfinite(emb).all()
+    cam = CP.CamPlus()
+    cam.load_state_dict({k: torch.from_numpy(v) for k, v in synth_weights.campplus_state(seed=3).items()}, strict=False)
+    cam.eval()
+    s3 = S3.S3Tokenizer(S3.S3Config(n_layer=2))
+    s3.load_state_dict({k: torch.from_numpy(v) for k, v in synth_weights.s3tok_state(cfg, seed=4).items()})
+    s3.eval()
+    off = np.concatenate([[0], np.cumsum(counts)])
+    total = bad = 0
+    for i in (0, 17, 128):
+        w = torch.from_numpy(utts[i].astype(np.float32) / 32768.0)[None]
+        ref = CP.embed_one(cam, F.cmn(F.kaldi_fbank(w)))
+        assert float(torch.nn.functional.cosine_similarity(emb[i], ref, dim=0)) >= 0.9999
+        ids = S3.tokenize_one(s3, F.whisper_log_mel(w))
+        got = tok[off[i]:off[i + 1]].tolist()
+        total += len(ids)
+        bad += sum(a != b for a, b in zip(got, ids))
+    assert bad / total <= 1e-3, (bad, total)
