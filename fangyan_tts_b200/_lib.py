@@ -2,9 +2,11 @@
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parent / "libfangyan_b200.so"
+# FY_LIB points at an alternative build of the same ABI (e.g. the stall-profiling build of tools/gemm_stalls.py)
+LIB_PATH = Path(os.environ.get("FY_LIB") or Path(__file__).resolve().parent / "libfangyan_b200.so")
 
 
 class FyTensor(C.Structure):

@@ -9,8 +9,11 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
-OBJ = HERE / "build"
-LIB = HERE / "libfangyan_b200.so"
+# FY_BUILD_TAG=prof FY_NVCC_EXTRA=-DFY_STALLPROF builds a side-by-side debug library (libfangyan_b200_prof.so) that
+# FY_LIB=<path> makes _lib.py load; the default build is untouched.
+_TAG = os.environ.get("FY_BUILD_TAG", "")
+OBJ = HERE / ("build_" + _TAG if _TAG else "build")
+LIB = HERE / ("libfangyan_b200_%s.so" % _TAG if _TAG else "libfangyan_b200.so")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -41,7 +44,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     def compile_one(src: Path):
         obj = OBJ / (src.stem + ".o")
         if force or _stale(obj, [src] + hdrs):
-            cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+            cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("FY_NVCC_EXTRA", "").split(), "-c", str(src), "-o", str(obj)]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             r = subprocess.run(cmd, capture_output=True, text=True)

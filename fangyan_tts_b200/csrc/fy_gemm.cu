@@ -51,18 +51,30 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 256 + 2 * BN * 4 + 1024;
 };
 
+// ex2 / rcp without the denormal fix-up sequences the default (non -ftz) intrinsics expand to
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_ftz(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // Exact (erf) GELU, x * Phi(x), with erfc from Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, below fp32 rounding of
 // the product): Phi(x) = h for x < 0 and 1 - h otherwise, h = 0.5 * poly(t) * exp(-x^2 / 2), t = 1 / (1 + p |x| / sqrt 2).
 // Evaluating h directly avoids the 1 + erf cancellation for negative x and costs two MUFU ops instead of erff's ~30
 // instructions, which is what kept the fc1 epilogue (5120 columns of GELU + hi/lo split) longer than its main loop.
 __device__ __forceinline__ float gelu_erf(float x) {
   const float z = fabsf(x) * 0.70710678118654752f;
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  const float t = rcp_ftz(fmaf(0.3275911f, z, 1.0f));
   float p = fmaf(t, 1.061405429f, -1.453152027f);
   p = fmaf(p, t, 1.421413741f);
   p = fmaf(p, t, -0.284496736f);
   p = fmaf(p, t, 0.254829592f);
-  const float h = 0.5f * p * t * __expf(-z * z);
+  const float h = 0.5f * p * t * ex2_ftz(z * z * -1.4426950408889634f);
   return x * (x < 0.0f ? h : 1.0f - h);
 }
 
@@ -71,8 +83,41 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// The epilogue holds one accumulator row per lane, so a plain 16-byte store touches 32 different rows (32 L1
+// wavefronts, 32 half-written sectors).  Transposing the four 16-byte pieces across each lane quad turns it into
+// 8 rows x 64 contiguous bytes: after the call, lane (Q + q) holds piece q of rows Q .. Q+3 in w[0..3].
+__device__ __forceinline__ uint4 shfl_xor_u4(uint4 v, int m) {
+  v.x = __shfl_xor_sync(0xffffffffu, v.x, m);
+  v.y = __shfl_xor_sync(0xffffffffu, v.y, m);
+  v.z = __shfl_xor_sync(0xffffffffu, v.z, m);
+  v.w = __shfl_xor_sync(0xffffffffu, v.w, m);
+  return v;
+}
+__device__ __forceinline__ void quad_transpose(uint4 (&w)[4], int lane) {
+  const bool b0 = lane & 1, b1 = lane & 2;
+#pragma unroll
+  for (int a = 0; a < 4; a += 2) {   // 2x2 blocks across lane bit 0: pieces (a, a+1)
+    const uint4 r = shfl_xor_u4(b0 ? w[a] : w[a + 1], 1);
+    if (b0) w[a] = r; else w[a + 1] = r;
+  }
+#pragma unroll
+  for (int a = 0; a < 2; ++a) {      // across lane bit 1: pieces (a, a+2)
+    const uint4 r = shfl_xor_u4(b1 ? w[a] : w[a + 2], 2);
+    if (b1) w[a] = r; else w[a + 2] = r;
+  }
+}
+
 // OP = OP_BF16 / OP_F16: 2-byte operands, 64-element K blocks (kind::f16).  OP = OP_TF32: fp32 data consumed as tf32,
 // 32-element K blocks (kind::tf32).  All are 128-byte rows, so tiles, swizzle and descriptors are identical.
+#ifdef FY_STALLPROF
+// Debug build only (tools/gemm_stalls.py): cycles each role spends blocked on its barrier, summed over CTAs.
+// slot = GEMM kind (0 QKV, 1 fc1, 2 O, 3 fc2, 4 other) x 8 counters.
+__device__ unsigned long long g_stall[5 * 8];
+#define FY_SP(...) __VA_ARGS__
+#else
+#define FY_SP(...)
+#endif
+
 template <int BN, int OP, int NCTA>
 __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) gemm_kernel(const __grid_constant__ GemmArgs args) {
   using C = Cfg<BN, NCTA>;
@@ -84,7 +129,7 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
   constexpr int BKE = TF32 ? 32 : 64;  // K elements per block
   constexpr int kEpiThreads = 32 * epi_warps<BN>();
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);   // stays a shared-space pointer
   uint8_t* tiles = smem;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
   uint64_t* empty_bar = full_bar + C::kStages;
@@ -101,6 +146,12 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
   const int num_m = (args.M + TM - 1) / TM;
   const int num_n = args.N / BN;
   const int num_tiles = num_m * num_n;
+#ifdef FY_STALLPROF
+  int sp_kb = 0;
+  for (int s = 0; s < args.nseg; ++s) sp_kb += args.seg[s].nkb;
+  const int sp_slot = 8 * (args.N == 3840 ? 0 : args.N == 5120 ? 1 : (args.N == 1280 && sp_kb == 60) ? 2
+                                                                      : (args.N == 1280 && sp_kb == 240) ? 3 : 4);
+#endif
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&args.tmap_a);
@@ -135,13 +186,16 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      FY_SP(long long sp_wait = 0; const long long sp_t0 = clock64();)
       for (int tile = worker; tile < num_tiles; tile += n_workers) {
         const int m0 = (tile / num_n) * TM + (int)cta_rank * BM;
         const int n0 = (tile % num_n) * BN + (int)cta_rank * (BN / NCTA);   // pair: this CTA's half of the B tile
         for (int s = 0; s < args.nseg; ++s) {
           const GemmSeg sg = args.seg[s];
           for (int kb = 0; kb < sg.nkb; ++kb) {
+            FY_SP(const long long sp_a = clock64();)
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            FY_SP(sp_wait += clock64() - sp_a;)
             uint8_t* a_dst = tiles + stage * C::kStageBytes;
             uint8_t* b_dst = a_dst + C::kABytes;
             if (PAIR) {
@@ -162,6 +216,8 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
           }
         }
       }
+      FY_SP(if (cta_rank == 0) { atomicAdd(&g_stall[sp_slot + 0], (unsigned long long)sp_wait);
+                                 atomicAdd(&g_stall[sp_slot + 1], (unsigned long long)(clock64() - sp_t0)); })
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
@@ -172,15 +228,20 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
+      FY_SP(long long sp_wf = 0, sp_we = 0; const long long sp_t0 = clock64();)
       for (int tile = worker; tile < num_tiles; tile += n_workers) {
+        FY_SP(const long long sp_a = clock64();)
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+        FY_SP(sp_we += clock64() - sp_a;)
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
         uint32_t accumulate = 0;
         for (int s = 0; s < args.nseg; ++s) {
           const int nkb = args.seg[s].nkb;
           for (int kb = 0; kb < nkb; ++kb) {
+            FY_SP(const long long sp_b = clock64();)
             ptx::mbar_wait(&full_bar[stage], phase);
+            FY_SP(sp_wf += clock64() - sp_b;)
             ptx::tc_fence_after();
             const uint32_t a_addr = ptx::smem_u32(tiles + stage * C::kStageBytes);
             const uint64_t da = ptx::make_desc_sw128(a_addr);
@@ -201,6 +262,9 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
         else ptx::mma_commit(&tfull_bar[as]);
         if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
       }
+      FY_SP(atomicAdd(&g_stall[sp_slot + 2], (unsigned long long)sp_wf);
+            atomicAdd(&g_stall[sp_slot + 3], (unsigned long long)sp_we);
+            atomicAdd(&g_stall[sp_slot + 4], (unsigned long long)(clock64() - sp_t0));)
     }
   } else if (warp >= 4) {
     // ===================== epilogue (warp w drains TMEM lane quarter w % 4; warps 8..11 take the upper columns) ====
@@ -212,6 +276,7 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
     int as = 0;
     uint32_t aphase = 0;
     int staged_n0 = -1;
+    FY_SP(long long sp_wt = 0; const long long sp_t0 = clock64();)
     for (int tile = worker; tile < num_tiles; tile += n_workers) {
       const int m0 = (tile / num_n) * TM + (int)cta_rank * BM;
       const int n0 = (tile % num_n) * BN;
@@ -237,7 +302,9 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
 #pragma unroll
         for (int j = 0; j < 4; ++j) rpre[j] = __ldg(rp + j);
       }
+      FY_SP(const long long sp_a = clock64();)
       ptx::mbar_wait(&tfull_bar[as], aphase);
+      FY_SP(sp_wt += clock64() - sp_a;)
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
       if (BN == 256 && e.mode == EPI_QKV_ROPE) {
@@ -245,62 +312,81 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
         const int which = n0 / e.rope_D;
         const int cbase = n0 - which * e.rope_D;
         __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(which == 0 ? e.out : (which == 1 ? e.out2 : e.out3));
-        __nv_bfloat16* o = ob + (size_t)row * e.ldo + cbase;
+        const int qrow0 = m0 + q * 32 + (lane & ~3);   // first row of this lane's quad (see quad_transpose)
+        const int qp = lane & 3;
         int pos = row_ok ? __ldg(e.rope_pos + row) : 0;
         if (pos < 0) pos = 0;
         const float* ct = e.rope_cos + (size_t)pos * 64;
         const float* sn = e.rope_sin + (size_t)pos * 64;
+        // Sub-chunk sc covers pair indices [16 sc, 16 sc + 16); its 16 cos / 16 sin values are loaded once (issued
+        // while the first head's TMEM load is in flight) and reused for every head this warp drains.
 #pragma unroll 1
-        for (int hs = 0; hs < kChunks; ++hs) {           // kChunks / 2 heads x 2 sub-chunks of 16 pairs
-          const int ca = c_begin * 32 + (hs >> 1) * 64 + (hs & 1) * 16;   // tile-local column of the first half
-          uint32_t va[16], vb[16];
-          ptx::tmem_ld_32x16(t_row + ca, va);
-          ptx::tmem_ld_32x16(t_row + ca + 32, vb);
-          ptx::tmem_ld_wait();
-          if (row_ok) {
-            float xa[16], xb[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              xa[j] = __uint_as_float(va[j]) + s_bias[ca + j];
-              xb[j] = __uint_as_float(vb[j]) + s_bias[ca + 32 + j];
-            }
-            if (which < 2) {
-              const int d0 = (hs & 1) * 16;
+        for (int sc = 0; sc < 2; ++sc) {
+          const int d0 = sc * 16;
+          float cc[16], ss[16];
+#pragma unroll 1
+          for (int hh = 0; hh < kChunks / 2; ++hh) {
+            const int ca = c_begin * 32 + hh * 64 + d0;     // tile-local column of the first half
+            uint32_t va[16], vb[16];
+            ptx::tmem_ld_32x16(t_row + ca, va);
+            ptx::tmem_ld_32x16(t_row + ca + 32, vb);
+            if (hh == 0 && which < 2) {
 #pragma unroll
               for (int j4 = 0; j4 < 4; ++j4) {
                 const float4 c4 = __ldg(reinterpret_cast<const float4*>(ct + d0) + j4);
                 const float4 s4 = __ldg(reinterpret_cast<const float4*>(sn + d0) + j4);
-                const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  const float a = xa[4 * j4 + k], b = xb[4 * j4 + k];
-                  xa[4 * j4 + k] = (a * cc[k] - b * ss[k]) * e.rope_scale;
-                  xb[4 * j4 + k] = (b * cc[k] + a * ss[k]) * e.rope_scale;
-                }
+                cc[4 * j4] = c4.x; cc[4 * j4 + 1] = c4.y; cc[4 * j4 + 2] = c4.z; cc[4 * j4 + 3] = c4.w;
+                ss[4 * j4] = s4.x; ss[4 * j4 + 1] = s4.y; ss[4 * j4 + 2] = s4.z; ss[4 * j4 + 3] = s4.w;
               }
             }
+            ptx::tmem_ld_wait();
+            {   // rows past M compute on zeros and are not stored; the quad shuffles need every lane
+              float xa[16], xb[16];
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              float* xs = half ? xb : xa;
-              uint4* dhi = reinterpret_cast<uint4*>(o + ca + half * 32);
-#pragma unroll
-              for (int j = 0; j < 2; ++j) {
-                uint4 w;
-                w.x = pack_bf16(xs[8 * j], xs[8 * j + 1]); w.y = pack_bf16(xs[8 * j + 2], xs[8 * j + 3]);
-                w.z = pack_bf16(xs[8 * j + 4], xs[8 * j + 5]); w.w = pack_bf16(xs[8 * j + 6], xs[8 * j + 7]);
-                dhi[j] = w;
+              for (int j = 0; j < 16; ++j) {
+                xa[j] = __uint_as_float(va[j]) + s_bias[ca + j];
+                xb[j] = __uint_as_float(vb[j]) + s_bias[ca + 32 + j];
               }
-              if (e.lo_col_off >= 0) {
-                uint4* dlo = reinterpret_cast<uint4*>(o + e.lo_col_off + ca + half * 32);
+              if (which < 2) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) xs[j] -= __bfloat162float(__float2bfloat16_rn(xs[j]));
-#pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                  uint4 w;
-                  w.x = pack_bf16(xs[8 * j], xs[8 * j + 1]); w.y = pack_bf16(xs[8 * j + 2], xs[8 * j + 3]);
-                  w.z = pack_bf16(xs[8 * j + 4], xs[8 * j + 5]); w.w = pack_bf16(xs[8 * j + 6], xs[8 * j + 7]);
-                  dlo[j] = w;
+                for (int j = 0; j < 16; ++j) {
+                  const float a = xa[j], b = xb[j];
+                  xa[j] = (a * cc[j] - b * ss[j]) * e.rope_scale;
+                  xb[j] = (b * cc[j] + a * ss[j]) * e.rope_scale;
                 }
+              }
+              // pieces [xa 0-7 | xa 8-15 | xb 0-7 | xb 8-15] of this row -> quad-transposed 2 x 32-byte runs per row
+              const int pcol = ca + (qp & 1) * 8 + (qp >> 1) * 32;
+              uint4 w[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float* xs = (j >> 1) ? xb : xa;
+                const int k = (j & 1) * 8;
+                w[j].x = pack_bf16(xs[k], xs[k + 1]); w[j].y = pack_bf16(xs[k + 2], xs[k + 3]);
+                w[j].z = pack_bf16(xs[k + 4], xs[k + 5]); w[j].w = pack_bf16(xs[k + 6], xs[k + 7]);
+              }
+              quad_transpose(w, lane);
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (qrow0 + j < args.M) *reinterpret_cast<uint4*>(ob + (size_t)(qrow0 + j) * e.ldo + cbase + pcol) = w[j];
+              if (e.lo_col_off >= 0) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  xa[j] -= __bfloat162float(__float2bfloat16_rn(xa[j]));
+                  xb[j] -= __bfloat162float(__float2bfloat16_rn(xb[j]));
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float* xs = (j >> 1) ? xb : xa;
+                  const int k = (j & 1) * 8;
+                  w[j].x = pack_bf16(xs[k], xs[k + 1]); w[j].y = pack_bf16(xs[k + 2], xs[k + 3]);
+                  w[j].z = pack_bf16(xs[k + 4], xs[k + 5]); w[j].w = pack_bf16(xs[k + 6], xs[k + 7]);
+                }
+                quad_transpose(w, lane);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (qrow0 + j < args.M)
+                    *reinterpret_cast<uint4*>(ob + (size_t)(qrow0 + j) * e.ldo + e.lo_col_off + cbase + pcol) = w[j];
               }
             }
           }
@@ -313,16 +399,36 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
         if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
         continue;
       }
+      // Affine rows (no row_idx, no remap: every S3 GEMM): global accesses are quad-transposed, see quad_transpose.
+      const bool fast = !e.row_idx && !e.remap_q;
+      const int qrow0 = m0 + q * 32 + (lane & ~3);   // first row of this lane's quad
+      const int qp = lane & 3;                       // the 16-byte piece this lane moves for each quad row
 #pragma unroll 1
       for (int c = c_begin; c < c_begin + kChunks; ++c) {
         uint32_t v[32];
         ptx::tmem_ld_32x32(t_row + c * 32, v);
-        ptx::tmem_ld_wait();
-        if (row_ok) {
-          float x[32];
-          const size_t col = (size_t)e.col_off + n0 + c * 32;
-          float rs[32];
-          if (e.resid) {
+        // Everything this chunk reads from global memory is requested while the TMEM load is in flight.
+        const size_t col = (size_t)e.col_off + n0 + c * 32;
+        float rs[32];
+        if (fast && e.mode == EPI_F32_ADD) {   // transposed layout: rs[16 g + 4 j ..] = piece 4 g + qp of row qrow0 + j
+          const float* ob = reinterpret_cast<const float*>(e.out) + col + qp * 4;
+#pragma unroll
+          for (int g = 0; g < 2; ++g)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (qrow0 + j < args.M) w = *reinterpret_cast<const float4*>(ob + (size_t)(qrow0 + j) * e.ldo + g * 16);
+              rs[16 * g + 4 * j] = w.x; rs[16 * g + 4 * j + 1] = w.y; rs[16 * g + 4 * j + 2] = w.z; rs[16 * g + 4 * j + 3] = w.w;
+            }
+        } else if (row_ok) {
+          if (e.mode == EPI_F32_ADD) {
+            const float4* rp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(e.out) + orow * e.ldo + col);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 w = rp[j];
+              rs[4 * j] = w.x; rs[4 * j + 1] = w.y; rs[4 * j + 2] = w.z; rs[4 * j + 3] = w.w;
+            }
+          } else if (e.resid) {
             const uint4* rp = reinterpret_cast<const uint4*>(e.resid + orow * e.ldo + col);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -340,8 +446,7 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
                 }
               }
             }
-          }
-          if (e.resid_f32) {
+          } else if (e.resid_f32) {
             const float4* rp = reinterpret_cast<const float4*>(e.resid_f32 + orow * e.ldo + col);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -349,14 +454,84 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
               rs[4 * j] = w.x; rs[4 * j + 1] = w.y; rs[4 * j + 2] = w.z; rs[4 * j + 3] = w.w;
             }
           }
+        }
+        ptx::tmem_ld_wait();
+        float x[32];
+        // One uniform branch per stage, never per element: the 32 columns stay independent instruction streams.
+        // Rows past M compute on zero accumulators (TMA zero-fills them) and are never stored.
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float t = __uint_as_float(v[j]) * s_scale[c * 32 + j] + s_bias[c * 32 + j];
-            if (e.resid || e.resid_f32) t += rs[j];
-            if (e.act == ACT_GELU) t = gelu_erf(t);
-            else if (e.act == ACT_RELU) t = fmaxf(t, 0.0f);
-            x[j] = t;
+        for (int j = 0; j < 32; ++j) x[j] = fmaf(__uint_as_float(v[j]), s_scale[c * 32 + j], s_bias[c * 32 + j]);
+        if ((e.resid || e.resid_f32) && e.mode != EPI_F32_ADD && row_ok) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] += rs[j];
+        }
+        if (e.act == ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = gelu_erf(x[j]);
+        } else if (e.act == ACT_RELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.0f);
+        }
+        if (fast) {
+          if (e.mode == EPI_BF16) {
+            char* ob = reinterpret_cast<char*>(e.out) + (col * 2 + qp * 16);
+            const size_t pitch = (size_t)e.ldo * 2;
+            uint4 w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (e.out_f16) {
+                w[j].x = pack_f16(x[8 * j], x[8 * j + 1]); w[j].y = pack_f16(x[8 * j + 2], x[8 * j + 3]);
+                w[j].z = pack_f16(x[8 * j + 4], x[8 * j + 5]); w[j].w = pack_f16(x[8 * j + 6], x[8 * j + 7]);
+              } else {
+                w[j].x = pack_bf16(x[8 * j], x[8 * j + 1]); w[j].y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
+                w[j].z = pack_bf16(x[8 * j + 4], x[8 * j + 5]); w[j].w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+              }
+            }
+            quad_transpose(w, lane);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (qrow0 + j < args.M) *reinterpret_cast<uint4*>(ob + (size_t)(qrow0 + j) * pitch) = w[j];
+            if (e.lo_col_off >= 0) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) x[j] -= __bfloat162float(__float2bfloat16_rn(x[j]));
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                w[j].x = pack_bf16(x[8 * j], x[8 * j + 1]); w[j].y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
+                w[j].z = pack_bf16(x[8 * j + 4], x[8 * j + 5]); w[j].w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+              }
+              quad_transpose(w, lane);
+              char* ol = ob + ((size_t)e.lo_col_off - (size_t)e.col_off) * 2;
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (qrow0 + j < args.M) *reinterpret_cast<uint4*>(ol + (size_t)(qrow0 + j) * pitch) = w[j];
+            }
+          } else {
+            if (e.round_tf32) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) x[j] = ptx::round_tf32(x[j]);
+            }
+            float* ob = reinterpret_cast<float*>(e.out) + col + qp * 4;
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+              uint4 w[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                w[j] = make_uint4(__float_as_uint(x[16 * g + 4 * j]), __float_as_uint(x[16 * g + 4 * j + 1]),
+                                  __float_as_uint(x[16 * g + 4 * j + 2]), __float_as_uint(x[16 * g + 4 * j + 3]));
+              quad_transpose(w, lane);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                float4 r = make_float4(__uint_as_float(w[j].x), __uint_as_float(w[j].y), __uint_as_float(w[j].z),
+                                       __uint_as_float(w[j].w));
+                if (e.mode == EPI_F32_ADD) {
+                  r.x += rs[16 * g + 4 * j]; r.y += rs[16 * g + 4 * j + 1];
+                  r.z += rs[16 * g + 4 * j + 2]; r.w += rs[16 * g + 4 * j + 3];
+                }
+                if (qrow0 + j < args.M) *reinterpret_cast<float4*>(ob + (size_t)(qrow0 + j) * e.ldo + g * 16) = r;
+              }
+            }
           }
+        } else if (row_ok) {
           if (e.row_gate && keep) {
             const float4* g = reinterpret_cast<const float4*>(e.row_gate + (size_t)ridx * args.N + n0 + c * 32);
 #pragma unroll
@@ -376,15 +551,11 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
             for (int j = 0; j < 4; ++j) {
               uint4 w;
               if (e.out_f16) {
-                w.x = pack_f16(x[8 * j], x[8 * j + 1]);
-                w.y = pack_f16(x[8 * j + 2], x[8 * j + 3]);
-                w.z = pack_f16(x[8 * j + 4], x[8 * j + 5]);
-                w.w = pack_f16(x[8 * j + 6], x[8 * j + 7]);
+                w.x = pack_f16(x[8 * j], x[8 * j + 1]); w.y = pack_f16(x[8 * j + 2], x[8 * j + 3]);
+                w.z = pack_f16(x[8 * j + 4], x[8 * j + 5]); w.w = pack_f16(x[8 * j + 6], x[8 * j + 7]);
               } else {
-                w.x = pack_bf16(x[8 * j], x[8 * j + 1]);
-                w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
-                w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]);
-                w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+                w.x = pack_bf16(x[8 * j], x[8 * j + 1]); w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
+                w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]); w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
               }
               dst[j] = w;
             }
@@ -395,10 +566,8 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 uint4 w;
-                w.x = pack_bf16(x[8 * j], x[8 * j + 1]);
-                w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
-                w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]);
-                w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
+                w.x = pack_bf16(x[8 * j], x[8 * j + 1]); w.y = pack_bf16(x[8 * j + 2], x[8 * j + 3]);
+                w.z = pack_bf16(x[8 * j + 4], x[8 * j + 5]); w.w = pack_bf16(x[8 * j + 6], x[8 * j + 7]);
                 dlo[j] = w;
               }
             }
@@ -410,11 +579,9 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
             float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow * e.ldo + col);
             if (e.mode == EPI_F32_ADD) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                float4 r = dst[j];
-                r.x += x[4 * j]; r.y += x[4 * j + 1]; r.z += x[4 * j + 2]; r.w += x[4 * j + 3];
-                dst[j] = r;
-              }
+              for (int j = 0; j < 8; ++j)
+                dst[j] = make_float4(rs[4 * j] + x[4 * j], rs[4 * j + 1] + x[4 * j + 1], rs[4 * j + 2] + x[4 * j + 2],
+                                     rs[4 * j + 3] + x[4 * j + 3]);
             } else {
 #pragma unroll
               for (int j = 0; j < 8; ++j) dst[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
@@ -429,6 +596,11 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
         }
       if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
     }
+    FY_SP(if (threadIdx.x == 128 && cta_rank == 0) {
+      atomicAdd(&g_stall[sp_slot + 5], (unsigned long long)sp_wt);
+      atomicAdd(&g_stall[sp_slot + 6], (unsigned long long)(clock64() - sp_t0));
+      atomicAdd(&g_stall[sp_slot + 7], 1ull);
+    })
   }
 
   ptx::tc_fence_before();
@@ -567,3 +739,16 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st) {
 }
 
 }  // namespace fy
+
+#ifdef FY_STALLPROF
+// Debug build only: copy the role-stall counters to the host (40 x u64) and optionally clear them.
+extern "C" int fy_debug_gemm_stalls(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  if (cudaMemcpyFromSymbol(out, fy::g_stall, sizeof(unsigned long long) * 40) != cudaSuccess) return 1;
+  if (reset) {
+    unsigned long long z[40] = {0};
+    if (cudaMemcpyToSymbol(fy::g_stall, z, sizeof(z)) != cudaSuccess) return 1;
+  }
+  return 0;
+}
+#endif
