@@ -56,12 +56,18 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+// 2^x without the denormal fix-up sequence exp2f expands to (results below 2^-126 flush to zero, as they should here)
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ float bf_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
 
 // q, k, v, out: bf16 [rows, ld] with head h at columns h*64 (hi) and lo_off + h*64 (lo, SPLIT only).
 // tiles: int2 (utt, q0) per blockIdx.x; utt_P / utt_L give the utterance's first row and length.
 template <bool SPLIT>
-__global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16* __restrict__ q,
+__global__ void __launch_bounds__(kThreads, 3) attention_kernel(const __nv_bfloat16* __restrict__ q,
                                                              const __nv_bfloat16* __restrict__ k,
                                                              const __nv_bfloat16* __restrict__ v,
                                                              __nv_bfloat16* __restrict__ out, int ld, int lo_off,
@@ -71,9 +77,10 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int NP = SPLIT ? 2 : 1;            // parts (hi, lo)
   constexpr int TILE = kBK * kDH * 2;          // 8 KB
-  // layout: Q[NP] | stage0: K[NP] V[NP] | stage1: K[NP] V[NP]
-  const uint32_t sQ = smem_u32(smem);
-  const uint32_t sKV = sQ + NP * TILE;
+  // layout: stage0: K[NP] V[NP] | stage1: K[NP] V[NP].  Q[NP] is staged in stage 1 and moved to registers before
+  // the first prefetch overwrites it (64 KB per CTA in SPLIT mode: three CTAs per SM).
+  const uint32_t sKV = smem_u32(smem);
+  const uint32_t sQ = sKV + 2 * NP * TILE;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int2 tl = tiles[blockIdx.x];
   const int u = tl.x, q0 = tl.y, h = blockIdx.y;
@@ -99,6 +106,19 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
   float mrow[2] = {-INFINITY, -INFINITY}, lrow[2] = {0.f, 0.f};
   const float kLog2e = 1.4426950408889634f;
 
+  // Q fragments -> registers, then stage 1 is free for the first prefetch
+  cp_wait<0>();
+  __syncthreads();
+#pragma unroll
+  for (int p = 0; p < NP; ++p)
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      const int row = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+      const int ch = ks * 2 + (lane >> 4);
+      ldsm_x4(tile_addr(sQ + p * TILE, row, ch), qf[p][ks][0], qf[p][ks][1], qf[p][ks][2], qf[p][ks][3]);
+    }
+  __syncthreads();
+
   for (int kt = 0; kt < nkt; ++kt) {
     const int st = kt & 1;
     if (kt + 1 < nkt) {
@@ -110,20 +130,10 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
         load_tile(sb + (NP + p) * TILE, v + (size_t)(P + k0n) * ld + col + p * lo_off, ld, min(kBK, L - k0n), tid);
       }
       cp_commit();
-      cp_wait<1>();
-    } else {
-      cp_wait<0>();
     }
-    __syncthreads();
-    if (kt == 0) {
-#pragma unroll
-      for (int p = 0; p < NP; ++p)
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {
-          const int row = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-          const int ch = ks * 2 + (lane >> 4);
-          ldsm_x4(tile_addr(sQ + p * TILE, row, ch), qf[p][ks][0], qf[p][ks][1], qf[p][ks][2], qf[p][ks][3]);
-        }
+    if (kt > 0) {   // tile 0 arrived with Q
+      if (kt + 1 < nkt) cp_wait<1>(); else cp_wait<0>();
+      __syncthreads();
     }
     const uint32_t sK = sKV + st * 2 * NP * TILE;
     const uint32_t sV = sK + NP * TILE;
@@ -162,13 +172,18 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
       }
     }
     // ---- mask keys beyond L, online softmax
-    const int kbase = kt * kBK + (lane & 3) * 2;
+    if ((kt + 1) * kBK > L) {   // only the last tile of an utterance can hold keys beyond L
+      const int kbase = kt * kBK + (lane & 3) * 2;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int kc = kbase + j * 8;
+        if (kc >= L) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
+        if (kc + 1 >= L) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
+      }
+    }
     float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int kc = kbase + j * 8;
-      if (kc >= L) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
-      if (kc + 1 >= L) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
       mx[0] = fmaxf(mx[0], fmaxf(s[j][0], s[j][1]));
       mx[1] = fmaxf(mx[1], fmaxf(s[j][2], s[j][3]));
     }
@@ -177,20 +192,23 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
       mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
       mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
     }
-    float corr[2], mnew[2];
+    // mrow holds the running maximum already scaled by log2(e): p = 2^(s log2e - mrow) with the product exact inside
+    // the FFMA, and the rescale 2^(mrow_old - mrow_new) uses the same rounded values, so every tile of a row is
+    // referenced consistently and the rounding of mrow cancels in the final division.
+    float corr[2], moff[2];
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
-      mnew[r] = fmaxf(mrow[r], mx[r]);
-      corr[r] = exp2f((mrow[r] - mnew[r]) * kLog2e);
-      mrow[r] = mnew[r];
+      moff[r] = fmaxf(mrow[r], mx[r] * kLog2e);    // finite: every tile holds at least one valid key
+      corr[r] = ex2(mrow[r] - moff[r]);
+      mrow[r] = moff[r];
     }
     float ls[2] = {0.f, 0.f};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      s[j][0] = exp2f((s[j][0] - mnew[0]) * kLog2e);
-      s[j][1] = exp2f((s[j][1] - mnew[0]) * kLog2e);
-      s[j][2] = exp2f((s[j][2] - mnew[1]) * kLog2e);
-      s[j][3] = exp2f((s[j][3] - mnew[1]) * kLog2e);
+    for (int j = 0; j < 8; ++j) {   // one FFMA + one MUFU per score
+      s[j][0] = ex2(fmaf(s[j][0], kLog2e, -moff[0]));
+      s[j][1] = ex2(fmaf(s[j][1], kLog2e, -moff[0]));
+      s[j][2] = ex2(fmaf(s[j][2], kLog2e, -moff[1]));
+      s[j][3] = ex2(fmaf(s[j][3], kLog2e, -moff[1]));
       ls[0] += s[j][0] + s[j][1];
       ls[1] += s[j][2] + s[j][3];
     }
@@ -271,7 +289,7 @@ __global__ void __launch_bounds__(kThreads) attention_kernel(const __nv_bfloat16
 }
 
 template <bool SPLIT>
-constexpr int smem_bytes() { return (SPLIT ? 2 : 1) * kBK * kDH * 2 * 5; }
+constexpr int smem_bytes() { return (SPLIT ? 2 : 1) * kBK * kDH * 2 * 4; }
 
 }  // namespace attn
 }  // namespace fy

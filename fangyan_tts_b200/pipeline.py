@@ -60,6 +60,7 @@ class Extractor:
         self.max_batch_seconds = max_batch_seconds
         self.max_batch_utts = max_batch_utts
         self._pin = None
+        self._copy_stream = None
 
     # ------------------------------------------------------------------ device-side preparation
     def _to_device_16k(self, utts: Sequence[Utt], mono: str):
@@ -148,7 +149,16 @@ class Extractor:
             for i, n in zip(idx, lens):
                 host[o:o + n] = utts[i].samples[:, 0]
                 o += n
-            pcm = self._pin[b0:o].to(self.eng.device, non_blocking=True)
+            # upload on a side stream: the copy of batch k+1 runs under the kernels of batch k
+            main = torch.cuda.current_stream(self.eng.device)
+            if self._copy_stream is None:
+                self._copy_stream = torch.cuda.Stream(self.eng.device)
+            with torch.cuda.stream(self._copy_stream):
+                pcm = self._pin[b0:o].to(self.eng.device, non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(self._copy_stream)
+            main.wait_event(ready)
+            pcm.record_stream(main)
             feat, frames = self.eng.fbank_cmn(pcm, lens)
             emb = self.eng.campplus(feat, frames)
             mel, mframes = self.eng.logmel(pcm, lens)
