@@ -41,6 +41,9 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=96, help="utterances in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-bf16-mode", action="store_true")
+    ap.add_argument("--frontend-sweep", action="store_true",
+                    help="BASELINE configs[4] instead of the headline step: front-end kernels only, batch 1-1024 of "
+                         "10 s clips against the HBM roofline, with the CPU restatement timed beside them")
     return ap.parse_args()
 
 
@@ -348,9 +351,37 @@ def run_reference(args):
     }))
 
 
+def run_frontend_sweep(args):
+    """One JSON line per batch size (tools/bench_frontend.py does the GPU side) and one `cpu_baseline` line: the oracle
+    front-ends (the reference's torchaudio / whisper / matcha calls restated) on 16 ten-second clips with every host
+    thread torch will use."""
+    import torch
+    sys.path.insert(0, str(Path(__file__).resolve().parent / "tools"))
+    import bench_frontend
+    bench_frontend.main()
+    from fangyan_tts_b200 import synth
+    from oracle import frontend as F
+    rng = np.random.default_rng(1986 + 4)
+    x16 = torch.from_numpy(synth.utterance(rng, 10.0).astype(np.float32) / 32768.0)[None]
+    x24 = F.resample(x16, 16000, 24000)
+    n, res = 16, {"config": "front-end sweep", "cpu_baseline": {"kind": "port", "cores": torch.get_num_threads(),
+                                                                   "sample": "16 x 10 s clips, batch 1 each"}}
+    for name, fn, x in (("fbank_cmn", lambda v: F.cmn(F.kaldi_fbank(v)), x16), ("logmel", F.whisper_log_mel, x16),
+                        ("matcha_mel_24k", F.matcha_mel, x24)):
+        fn(x)
+        t0 = time.perf_counter()
+        for _ in range(n):
+            fn(x)
+        dt = time.perf_counter() - t0
+        res["cpu_baseline"][name] = {"ms_per_clip": 1e3 * dt / n, "audio_hours_per_s": n * 10.0 / 3600.0 / dt}
+    print(json.dumps(res), flush=True)
+
+
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
+    if a.frontend_sweep:
+        run_frontend_sweep(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)

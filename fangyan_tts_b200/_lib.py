@@ -40,6 +40,7 @@ PROTOTYPES = {
     "fy_fbank_cmn": (_I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _Z]),
     "fy_logmel_workspace_bytes": (_Z, [_I, _I]),
     "fy_logmel": (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _P, _P, _Z]),
+    "fy_matcha_mel": (_I, [_P, _P, _I, _P, _P, _I, _I, _P]),
     "fy_campplus_workspace_bytes": (_Z, [_P, _I, _I]),
     "fy_campplus_forward": (_I, [_P, _P, _P, _P, _I, _P, _P, _Z]),
     "fy_campplus_layout": (_I, [_P, _P, _I, _P, _I]),

@@ -122,6 +122,12 @@ struct Ctx {
   int* wh_mel_len = nullptr;
   int* wh_mel_ptr = nullptr;
   float2* wh_tw = nullptr;         // [400] twiddles for N=400
+  float* mm_window = nullptr;      // [1920] hann periodic (matcha 24 kHz mel)
+  float* mm_mel_w = nullptr;
+  int* mm_mel_off = nullptr;
+  int* mm_mel_len = nullptr;
+  int* mm_mel_ptr = nullptr;
+  float2* mm_tw = nullptr;         // [1920] twiddles for N=1920
   // model weights (device, owned)
   std::map<std::string, Tensor> cam_w;
   std::map<std::string, Tensor> s3_w;

@@ -24,12 +24,13 @@ __device__ __forceinline__ float2 mul_negi(float2 a) { return make_float2(a.y, -
 
 // One Stockham stage of radix R over a length-N transform whose previous radices multiply to s.
 //   y[q + s*(R*p + k)] = w^(k) * sum_j x[q + s*(p + m*j)] * exp(-2 pi i jk/R),  w = exp(-2 pi i p s / N)
-template <int N, int R>
+// NT cooperating threads: 32 = one warp (__syncwarp between stages), otherwise the whole block (__syncthreads).
+template <int N, int R, int NT = 32>
 __device__ __forceinline__ void fft_stage(const float2* __restrict__ x, float2* __restrict__ y, int s,
                                           const float2* __restrict__ tw, int lane) {
   constexpr int NB = N / R;
   const int m = NB / s;
-  for (int i = lane; i < NB; i += 32) {
+  for (int i = lane; i < NB; i += NT) {
     const int q = i % s;
     const int p = i / s;
     float2 a[R];
@@ -46,6 +47,11 @@ __device__ __forceinline__ void fft_stage(const float2* __restrict__ x, float2* 
       b[1] = cadd(t1, t3);
       b[2] = csub(t0, t2);
       b[3] = csub(t1, t3);
+    } else if (R == 3) {
+      const float2 w1 = make_float2(-0.5f, -0.86602540378443865f), w2 = make_float2(-0.5f, 0.86602540378443865f);
+      b[0] = cadd(a[0], cadd(a[1], a[2]));
+      b[1] = cadd(a[0], cadd(cmul(a[1], w1), cmul(a[2], w2)));
+      b[2] = cadd(a[0], cadd(cmul(a[1], w2), cmul(a[2], w1)));
     } else {  // R == 5, direct
       const float c1 = 0.30901699437494745f, s1 = 0.95105651629515353f;
       const float c2 = -0.80901699437494734f, s2 = 0.58778525229247314f;
@@ -66,7 +72,7 @@ __device__ __forceinline__ void fft_stage(const float2* __restrict__ x, float2* 
 #pragma unroll
     for (int k = 1; k < R; ++k) y[base + s * k] = (m == 1) ? b[k] : cmul(b[k], tw[(step * k) % N]);
   }
-  __syncwarp();
+  if (NT == 32) __syncwarp(); else __syncthreads();
 }
 
 // 512-point: result ends in `a` when the number of stages is odd (5 stages: a->b->a->b->a->b ... see below).
@@ -344,6 +350,78 @@ __global__ void __launch_bounds__(256) logmel_finish_kernel(const float* __restr
   }
 }
 
+// ------------------------------------------------------------------------------------------ matcha 24 kHz mel
+// matcha.utils.audio.mel_spectrogram(n_fft 1920, hop 480, win 1920, 80 mels, fmin 0, fmax None, center=False)
+// (third_party/Matcha-TTS/matcha/utils/audio.py:44-88): reflect-pad 720 samples each side, periodic Hann, |STFT| =
+// sqrt(re^2 + im^2 + 1e-9), Slaney mel, log(max(., 1e-5)).  Output time-major [frames, 80] (both reference callers
+// transpose to that: frontend.py:122, processor.py:174).  One block of 128 threads per frame pair of ONE utterance
+// (pair slots as in find_slot_utt); the 1920-point complex transform (radix 4.4.4.5.3.2) carries two real frames.
+constexpr int kMmN = 1920, kMmHop = 480, kMmPad = 720, kMmBins = 961, kMmMels = 80, kMmThreads = 128;
+template <bool S16>
+__global__ void __launch_bounds__(kMmThreads) matcha_mel_kernel(const void* __restrict__ pcm,
+                                                                const int* __restrict__ pcm_off,
+                                                                const int* __restrict__ frame_off, int n_utts,
+                                                                int total_frames, const float* __restrict__ window,
+                                                                const float2* __restrict__ tw, MelTable mt,
+                                                                float* __restrict__ out) {
+  __shared__ float2 A[kMmN];
+  __shared__ float2 B[kMmN];
+  const int tid = threadIdx.x;
+  const int slot = blockIdx.x;
+  if (slot >= ((total_frames + n_utts) >> 1)) return;
+  const int u = find_slot_utt(frame_off, n_utts, slot);
+  const int fo = __ldg(frame_off + u);
+  const int f0 = 2 * (slot - ((fo + u) >> 1));
+  const int nf = __ldg(frame_off + u + 1) - fo;
+  if (f0 >= nf) return;
+  const int base = __ldg(pcm_off + u);
+  const int ns = __ldg(pcm_off + u + 1) - base;
+  const bool two = f0 + 1 < nf;
+  for (int i = tid; i < kMmN; i += kMmThreads) {
+    const float w = __ldg(window + i);
+    float2 v = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int f = 0; f < 2; ++f) {
+      if (f == 0 || two) {
+        int idx = (f0 + f) * kMmHop + i - kMmPad;
+        if (idx < 0) idx = -idx;
+        if (idx >= ns) idx = 2 * (ns - 1) - idx;
+        idx = max(0, min(idx, ns - 1));
+        const float x = load_pcm<S16>(pcm, base + idx) * w;
+        if (f == 0) v.x = x; else v.y = x;
+      }
+    }
+    A[i] = v;
+  }
+  __syncthreads();
+  fft_stage<kMmN, 4, kMmThreads>(A, B, 1, tw, tid);
+  fft_stage<kMmN, 4, kMmThreads>(B, A, 4, tw, tid);
+  fft_stage<kMmN, 4, kMmThreads>(A, B, 16, tw, tid);
+  fft_stage<kMmN, 5, kMmThreads>(B, A, 64, tw, tid);
+  fft_stage<kMmN, 3, kMmThreads>(A, B, 320, tw, tid);
+  fft_stage<kMmN, 2, kMmThreads>(B, A, 960, tw, tid);
+  float* P = reinterpret_cast<float*>(B);   // magnitudes: P[k] frame 0, P[961 + k] frame 1
+  for (int k = tid; k < kMmBins; k += kMmThreads) {
+    const float2 z = A[k];
+    const float2 zc = A[k == 0 ? 0 : kMmN - k];
+    const float ar = 0.5f * (z.x + zc.x), ai = 0.5f * (z.y - zc.y);
+    const float br = 0.5f * (z.y + zc.y), bi = -0.5f * (z.x - zc.x);
+    P[k] = sqrtf(ar * ar + ai * ai + 1e-9f);
+    P[kMmBins + k] = sqrtf(br * br + bi * bi + 1e-9f);
+  }
+  __syncthreads();
+  for (int o = tid; o < 2 * kMmMels; o += kMmThreads) {
+    const int f = o / kMmMels, b = o - f * kMmMels;
+    if (f == 1 && !two) continue;
+    const int off = __ldg(mt.off + b), n = __ldg(mt.len + b);
+    const float* w = mt.w + __ldg(mt.ptr + b);
+    const float* p = P + f * kMmBins + off;
+    float acc = 0.f;
+    for (int j = 0; j < n; ++j) acc = fmaf(__ldg(w + j), p[j], acc);
+    out[(size_t)(fo + f0 + f) * kMmMels + b] = logf(fmaxf(acc, 1e-5f));
+  }
+}
+
 // ------------------------------------------------------------------------------------------ resample
 __global__ void resample_kernel(const float* __restrict__ in, const int* __restrict__ in_off, float* __restrict__ out,
                                 const int* __restrict__ out_off, int n_utts, int total_out,
@@ -427,9 +505,9 @@ std::vector<std::vector<float>> kaldi_bank() {
 }
 
 // librosa.filters.mel(sr=16000, n_fft=400, n_mels=128): Slaney scale, Slaney area normalisation, float64 maths.
-std::vector<std::vector<float>> slaney_bank() {
-  const int nm = 128, nfft = 400, nf = nfft / 2 + 1;
-  const double sr = 16000.0, f_sp = 200.0 / 3, min_log_hz = 1000.0, min_log_mel = min_log_hz / f_sp;
+std::vector<std::vector<float>> slaney_bank(int nm = 128, int nfft = 400, double sr = 16000.0) {
+  const int nf = nfft / 2 + 1;
+  const double f_sp = 200.0 / 3, min_log_hz = 1000.0, min_log_mel = min_log_hz / f_sp;
   const double logstep = log(6.4) / 27.0;
   auto hz2mel = [&](double f) { return f >= min_log_hz ? min_log_mel + log(f / min_log_hz) / logstep : f / f_sp; };
   auto mel2hz = [&](double m) { return m >= min_log_mel ? min_log_hz * exp(logstep * (m - min_log_mel)) : f_sp * m; };
@@ -467,6 +545,12 @@ int frontend_init(Ctx* c) {
   FY_TRY(upload(c, twiddles(400), &c->wh_tw));
   FY_TRY(upload_mel(c, kaldi_bank(), &c->fb_mel_w, &c->fb_mel_off, &c->fb_mel_len, &c->fb_mel_ptr));
   FY_TRY(upload_mel(c, slaney_bank(), &c->wh_mel_w, &c->wh_mel_off, &c->wh_mel_len, &c->wh_mel_ptr));
+  // matcha 24 kHz mel (row N4): periodic Hann(1920), 1920-point twiddles, librosa mel(sr 24000, n_fft 1920, 80)
+  std::vector<float> hann24(kMmN);
+  for (int i = 0; i < kMmN; ++i) hann24[i] = (float)(0.5 - 0.5 * cos(2.0 * M_PI * i / (double)kMmN));
+  FY_TRY(upload(c, hann24, &c->mm_window));
+  FY_TRY(upload(c, twiddles(kMmN), &c->mm_tw));
+  FY_TRY(upload_mel(c, slaney_bank(kMmMels, kMmN, 24000.0), &c->mm_mel_w, &c->mm_mel_off, &c->mm_mel_len, &c->mm_mel_ptr));
   return FY_OK;
 }
 
@@ -547,6 +631,26 @@ int fy_logmel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_of
   dim3 grid((max_frames + 31) / 32, n_utts);
   logmel_finish_kernel<<<grid, 256, 0, c->stream>>>(raw, frame_off, umax, mel);
   c->launches += 3;
+  FY_CUDA(cudaGetLastError());
+  return FY_OK;
+}
+
+int fy_matcha_mel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
+                  int n_utts, int total_frames, float* mel) {
+  FY_CHECK(ctx && pcm && pcm_off && frame_off && mel, FY_ERR_ARG, "fy_matcha_mel: NULL argument");
+  FY_CHECK(n_utts > 0 && total_frames >= 0, FY_ERR_ARG, "fy_matcha_mel: bad sizes");
+  FY_CHECK(pcm_dtype == FY_PCM_S16 || pcm_dtype == FY_PCM_F32, FY_ERR_ARG, "fy_matcha_mel: bad pcm dtype");
+  if (total_frames == 0) return FY_OK;
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  MelTable mt{c->mm_mel_w, c->mm_mel_off, c->mm_mel_len, c->mm_mel_ptr};
+  const int pairs = ((total_frames + n_utts) >> 1) + 1;
+  if (pcm_dtype == FY_PCM_S16)
+    matcha_mel_kernel<true><<<pairs, kMmThreads, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,
+                                                               c->mm_window, c->mm_tw, mt, mel);
+  else
+    matcha_mel_kernel<false><<<pairs, kMmThreads, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,
+                                                                c->mm_window, c->mm_tw, mt, mel);
+  c->launches += 1;
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }

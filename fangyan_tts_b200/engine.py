@@ -25,6 +25,14 @@ def whisper_num_frames(n: int) -> int:
     return n // 160
 
 
+MATCHA_PAD = 720   # (n_fft - hop) / 2 of the 24 kHz mel
+
+
+def matcha_num_frames(n: int) -> int:
+    """Frames of matcha mel_spectrogram(n_fft 1920, hop 480, center=False) after its 720 + 720 reflect padding."""
+    return 1 + (n - 480) // 480 if n >= 480 else 0
+
+
 def token_len(t: int) -> int:
     """Two Conv1d(k=3, s=2, p=1) in the S3 encoder."""
     l1 = (t - 1) // 2 + 1
@@ -171,6 +179,23 @@ class Engine:
         ws = self.workspace(nb)
         check(self.lib.fy_logmel(self.h, _ptr(pcm), self._pcm_dtype(pcm), _ptr(d_po), _ptr(d_fo), len(lengths), total,
                                  max(frames) if frames else 0, _ptr(mel), _ptr(ws), ws.numel()))
+        return mel, frames
+
+    # ------------------------------------------------------------------ N4: 24 kHz matcha mel
+    def matcha_mel(self, pcm: torch.Tensor, lengths: Sequence[int]):
+        """24 kHz packed PCM -> (mel packed fp32 [sum T_b, 80] time-major, frame counts).  The reference's
+        feat_extractor (matcha mel_spectrogram, n_fft 1920 / hop 480 / center=False) followed by its callers'
+        transpose(0, 1): cosyvoice/cli/frontend.py:120-125, cosyvoice/dataset/processor.py:156-181."""
+        for i, n in enumerate(lengths):
+            if n <= MATCHA_PAD:   # torch's reflect padding refuses these too
+                raise ValueError(f"utterance {i}: {n} samples at 24 kHz, need more than {MATCHA_PAD} for reflect padding")
+        frames = [matcha_num_frames(n) for n in lengths]
+        pcm_off, fr_off = _offsets(lengths), _offsets(frames)
+        total = int(fr_off[-1])
+        mel = torch.empty((total, 80), dtype=torch.float32, device=self.device)
+        d_po, d_fo = self._dev_i32(pcm_off), self._dev_i32(fr_off)
+        check(self.lib.fy_matcha_mel(self.h, _ptr(pcm), self._pcm_dtype(pcm), _ptr(d_po), _ptr(d_fo), len(lengths),
+                                     total, _ptr(mel)))
         return mel, frames
 
     # ------------------------------------------------------------------ A6

@@ -3,6 +3,7 @@
 Mirrors cosyvoice/cli/frontend.py:95-118 of the reference (method names, argument meaning, return types, asserts):
     _extract_speech_token(prompt_wav)  -> (int32 [1, L], int32 [1]) on the device; asserts the clip is <= 30 s
     _extract_spk_embedding(prompt_wav) -> float32 [1, 192] on the device
+    _extract_speech_feat(prompt_wav)   -> (float32 [1, T, 80], int32 [1]) on the device (24 kHz matcha mel, row N4)
 and its loader cosyvoice/utils/file_utils.py:44-50 (channel MEAN first, then resample; sample rate must be >= 16 kHz)
 -- note this differs from the stage CLIs, which take channel 0 for stage 1.
 """
@@ -56,3 +57,11 @@ class CosyVoiceFrontEndB200:
         speech = self.load_wav(prompt_wav, SR)
         feat, frames = self.engine.fbank_cmn(speech, [speech.numel()])
         return self.engine.campplus(feat, frames).view(1, -1)
+
+    def _extract_speech_feat(self, prompt_wav):
+        """frontend.py:120-125: load at 24 kHz -> matcha mel -> (float32 [1, T, 80], int32 [1]) on the device."""
+        speech = self.load_wav(prompt_wav, 24000)
+        mel, frames = self.engine.matcha_mel(speech, [speech.numel()])
+        speech_feat = mel.view(1, frames[0], 80)
+        speech_feat_len = torch.tensor([speech_feat.shape[1]], dtype=torch.int32, device=self.device)
+        return speech_feat, speech_feat_len

@@ -101,6 +101,16 @@ size_t fy_logmel_workspace_bytes(int n_utts, int total_frames);
 int fy_logmel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
               int n_utts, int total_frames, int max_frames, float* mel, void* ws, size_t ws_bytes);
 
+/* ---- N4: matcha.utils.audio.mel_spectrogram at 24 kHz --------------------------------
+ * The `feat_extractor` of cosyvoice/cli/frontend.py:120-125 (_extract_speech_feat) and of the training loader
+ * (cosyvoice/dataset/processor.py:156-181 compute_fbank; conf/cosyvoice3.yaml:140-151): n_fft 1920, hop 480,
+ * win 1920, 80 mels, fmin 0, fmax None, center=False (third_party/Matcha-TTS/matcha/utils/audio.py:44-88).
+ * pcm: packed mono 24 kHz samples (int16 or float32), every utterance longer than 720 samples (reflect padding).
+ * mel: packed time-major [sum T_b, 80] fp32 -- what both callers use after their transpose(0, 1);
+ * T_b = 1 + (N_b - 480) / 480; frame_off = prefix sums of T_b. */
+int fy_matcha_mel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
+                  int n_utts, int total_frames, float* mel);
+
 /* ---- A6: ort_session.run(None, {"input": feat[None]}) on campplus.onnx ------------------------------------
  * tools/extract_embedding.py:36-41, cosyvoice/cli/frontend.py:115-116.
  * feat: packed [sum M_b, 80] fp32 (output of fy_fbank_cmn); emb: [n_utts, 192] fp32. */

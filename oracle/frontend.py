@@ -225,6 +225,32 @@ def whisper_log_mel(audio: torch.Tensor) -> torch.Tensor:
     return (log_spec + 4.0) / 4.0
 
 
+# ----------------------------------------------------------------------------- N4 matcha 24 kHz mel
+
+MATCHA_SR, MATCHA_NFFT, MATCHA_HOP, MATCHA_MELS = 24000, 1920, 480, 80
+
+
+def matcha_mel(audio: torch.Tensor) -> torch.Tensor:
+    """[1, N] float32 at 24 kHz -> [1, 80, T] float32, T = 1 + (N - 480) // 480.
+
+    Restates matcha.utils.audio.mel_spectrogram(y, n_fft=1920, num_mels=80, sampling_rate=24000, hop_size=480,
+    win_size=1920, fmin=0, fmax=None, center=False) (third_party/Matcha-TTS/matcha/utils/audio.py:44-88), the
+    `feat_extractor` of conf/cosyvoice3.yaml:140-151 called at cosyvoice/cli/frontend.py:122 and
+    cosyvoice/dataset/processor.py:174: reflect-pad (n_fft - hop) / 2 on both sides, periodic-Hann STFT without
+    centring, sqrt(re^2 + im^2 + 1e-9), librosa Slaney mel basis, log(clamp(., 1e-5)).
+    Pinned by tests/test_oracle_cpu.py against that function itself (imported from /root/reference with
+    librosa.filters.mel supplied by slaney_mel_filters, itself pinned on transformers' mel_filter_bank) and by the
+    golden vectors tests/golden/matcha.npz generated the same way."""
+    pad = (MATCHA_NFFT - MATCHA_HOP) // 2
+    y = torch.nn.functional.pad(audio.unsqueeze(1), (pad, pad), mode="reflect").squeeze(1)
+    spec = torch.stft(y, MATCHA_NFFT, hop_length=MATCHA_HOP, win_length=MATCHA_NFFT,
+                      window=torch.hann_window(MATCHA_NFFT), center=False, normalized=False, onesided=True,
+                      return_complex=True)
+    mag = torch.sqrt(spec.real ** 2 + spec.imag ** 2 + 1e-9)
+    basis = torch.from_numpy(slaney_mel_filters(MATCHA_MELS, MATCHA_NFFT, MATCHA_SR))
+    return torch.log(torch.clamp(basis @ mag, min=1e-5))
+
+
 # ----------------------------------------------------------------------------- A8 gate
 
 

@@ -44,6 +44,25 @@ def main():
             gbs = bytes_per_s * secs / (ms * 1e-3) / 1e9
             res[name] = {"ms": ms, "achieved_GBps": gbs, "frac_of_measured_hbm": gbs / hbm,
                          "audio_hours_per_s": secs / 3600.0 / (ms * 1e-3)}
+        # row N4: 24 kHz matcha mel on the same number of 10 s clips (48,000 B int16 in + 16,000 B mel out per audio-s)
+        base24 = np.resize(base, 240000)
+        sets24 = [torch.from_numpy(np.tile(np.roll(base24, 37 * k), batch)).cuda() for k in range(min(n_sets, 8))]
+        lens24 = [len(base24)] * batch
+        for k in range(3):
+            eng.matcha_mel(sets24[k % len(sets24)], lens24)
+        iters = max(5, min(50, int(2000 / batch) + 5))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for k in range(iters):
+            eng.matcha_mel(sets24[k % len(sets24)], lens24)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / iters
+        gbs = 64000.0 * secs / (ms * 1e-3) / 1e9
+        res["matcha_mel_24k"] = {"ms": ms, "achieved_GBps": gbs, "frac_of_measured_hbm": gbs / hbm,
+                                 "audio_hours_per_s": secs / 3600.0 / (ms * 1e-3)}
+        del sets24
         print(json.dumps(res), flush=True)
 
 
