@@ -41,6 +41,9 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=96, help="utterances in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-bf16-mode", action="store_true")
+    ap.add_argument("--stage3-pack", type=int, default=0, metavar="N",
+                    help="row N1 instead of the headline step: pack N synthetic utterances into parquet shards with "
+                         "the Arrow-direct writer and with the reference's pandas path (CPU only), one JSON line")
     ap.add_argument("--frontend-sweep", action="store_true",
                     help="BASELINE configs[4] instead of the headline step: front-end kernels only, batch 1-1024 of "
                          "10 s clips against the HBM roofline, with the CPU restatement timed beside them")
@@ -377,9 +380,59 @@ def run_frontend_sweep(args):
     print(json.dumps(res), flush=True)
 
 
+def run_stage3_pack(args):
+    """Row N1: wall time from the stage-1/2 outputs on disk to parquet shards, reference path (torch.load of the list
+    pickles + pandas frames of Python lists, oracle/stage3.py) against parquet_pack (sidecars + Arrow arrays)."""
+    import tempfile
+    import wave
+    from fangyan_tts_b200 import kaldi_io, parquet_pack
+    from oracle import stage3
+    n = args.stage3_pack
+    rng = np.random.default_rng(7)
+    with tempfile.TemporaryDirectory() as tmp:
+        src = Path(tmp) / "src"
+        src.mkdir()
+        keys = [f"utt{i:07d}" for i in range(n)]
+        wavp = src / "clip.wav"                               # one small clip shared by every row: IO is not the subject
+        with wave.open(str(wavp), "wb") as w:
+            w.setnchannels(1); w.setsampwidth(2); w.setframerate(16000)
+            w.writeframes(rng.integers(-3000, 3000, 16000, dtype=np.int16).tobytes())
+        utt2spk = {k: f"spk{i % 200:03d}" for i, k in enumerate(keys)}
+        with open(src / "wav.scp", "w") as f1, open(src / "text", "w") as f2, open(src / "utt2spk", "w") as f3:
+            for k in keys:
+                f1.write(f"{k} {wavp}\n"); f2.write(f"{k} some text of {k}\n"); f3.write(f"{k} {utt2spk[k]}\n")
+        emb = rng.standard_normal((n, 192)).astype(np.float32)
+        spk_names = sorted(set(utt2spk.values()))
+        semb = rng.standard_normal((len(spk_names), 192)).astype(np.float32)
+        toks = [rng.integers(0, 6561, int(rng.integers(75, 250))).astype(np.int32) for _ in range(n)]
+        kaldi_io.save_atomic(kaldi_io.embeddings_to_dict(keys, emb), src / "utt2embedding.pt")
+        kaldi_io.save_atomic(kaldi_io.speaker_dict(spk_names, semb), src / "spk2embedding.pt")
+        kaldi_io.save_atomic({k: t.tolist() for k, t in zip(keys, toks)}, src / "utt2speech_token.pt")
+        parquet_pack.write_embedding_sidecar(src / parquet_pack.EMB_SIDECAR, keys, emb)
+        parquet_pack.write_embedding_sidecar(src / parquet_pack.SPK_SIDECAR, spk_names, semb)
+        parquet_pack.write_token_sidecar(src / parquet_pack.TOK_SIDECAR, keys, toks)
+        t0 = time.perf_counter()
+        parquet_pack.make_parquet_list(str(src), str(Path(tmp) / "ours"), 1000, 1)
+        ours = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        utt2wav = kaldi_io.read_table(str(src / "wav.scp"))
+        utt2text = {k: f"some text of {k}" for k in keys}
+        e, s, k = stage3.load_pt(str(src))
+        (Path(tmp) / "ref").mkdir()
+        for i, j in enumerate(range(0, n, 1000)):
+            stage3.job(keys[j:j + 1000], str(Path(tmp) / "ref" / f"parquet_{i:09d}.tar"), utt2wav, utt2text, utt2spk, e, s, k)
+        ref = time.perf_counter() - t0
+    print(json.dumps({"metric": "stage3_pack_utts_per_sec", "unit": "utterances/s", "utts": n, "workers": 1,
+                      "value": n / ours, "seconds": ours,
+                      "cpu_baseline": {"kind": "port", "value": n / ref, "seconds": ref, "cores": 1,
+                                       "sample": f"{n} synthetic utterances, 1,000 per shard"}}), flush=True)
+
+
 if __name__ == "__main__":
     a = parse_args()
-    if a.frontend_sweep:
+    if a.stage3_pack:
+        run_stage3_pack(a)
+    elif a.frontend_sweep:
         run_frontend_sweep(a)
     elif a.impl == "reference":
         run_reference(a)

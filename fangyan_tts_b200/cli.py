@@ -34,7 +34,7 @@ from typing import List, Sequence
 
 import numpy as np
 
-from . import kaldi_io
+from . import kaldi_io, parquet_pack
 
 SR = 16000
 log = logging.getLogger("fangyan_b200")
@@ -164,6 +164,11 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
                                  os.path.join(args.dir, "utt2embedding.pt"))
             kaldi_io.save_atomic(kaldi_io.speaker_dict(spk_names, mean.cpu().numpy()),
                                  os.path.join(args.dir, "spk2embedding.pt"))
+            if os.environ.get("FY_SIDECAR", "1") != "0":      # compact copies for the Arrow stage-3 fast path
+                parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.EMB_SIDECAR), keys,
+                                                     full.cpu().numpy())
+                parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.SPK_SIDECAR), spk_names,
+                                                     mean.cpu().numpy())
     else:
         gated = [i for i in mine if n16[i] / SR > 30]          # extract_speech_token.py:34-36: key kept, value []
         for i in gated:
@@ -185,6 +190,9 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         if rank == 0:
             out = {k: ([] if p is None else p.cpu().tolist()) for k, p in zip(keys, per_utt)}
             kaldi_io.save_atomic(out, os.path.join(args.dir, "utt2speech_token.pt"))
+            if os.environ.get("FY_SIDECAR", "1") != "0":
+                parquet_pack.write_token_sidecar(os.path.join(args.dir, parquet_pack.TOK_SIDECAR), keys,
+                                                 [None if p is None else p.cpu().numpy() for p in per_utt])
     torch.cuda.synchronize()
     if rank == 0:
         wall = time.perf_counter() - t_start

@@ -102,6 +102,34 @@ def test_extract_speech_token_cli(data_dir):
     assert bad / total <= 1e-3, (bad, total)
 
 
+def test_cli_outputs_feed_stage3(data_dir, tmp_path):
+    """Row N1: the sidecars the CLIs leave hold exactly the .pt values, and the Arrow stage-3 writer fed by them
+    produces the shard the reference's pandas job produces from the .pt files."""
+    import pyarrow.parquet as pq
+    from fangyan_tts_b200 import parquet_pack
+    from oracle import stage3
+    d, keys, utts, st = data_dir
+    if not (d / "utt2embedding.pt").exists():
+        _run("extract_embedding.py", d, d / "campplus.npz")
+    if not (d / "utt2speech_token.pt").exists():
+        _run("extract_speech_token.py", d, d / "s3tok.npz", {"FY_S3TOK_CONFIG": str(d / "s3.json")})
+    e, sp, tk = stage3.load_pt(str(d))
+    z = np.load(d / parquet_pack.EMB_SIDECAR)
+    assert [str(k) for k in z["keys"]] == list(e) and np.array_equal(z["emb"], np.array([e[k] for k in e], dtype=np.float32))
+    z = np.load(d / parquet_pack.TOK_SIDECAR)
+    assert [str(k) for k in z["keys"]] == list(tk)
+    assert z["flat"].tolist() == [t for k in tk for t in tk[k]]
+    with open(d / "text", "w") as f:
+        for k in keys:
+            f.write(f"{k} text of {k}\n")
+    parquet_pack.make_parquet_list(str(d), str(tmp_path / "pq"), 1000, 2)
+    rd = lambda name: {l.split()[0]: " ".join(l.split()[1:]) for l in open(d / name)}
+    stage3.job(list(rd("wav.scp")), tmp_path / "ref.parquet", rd("wav.scp"), rd("text"), rd("utt2spk"), e, sp, tk)
+    a = pq.read_table(tmp_path / "pq" / "parquet_000000000.tar")
+    b = pq.read_table(tmp_path / "ref.parquet").replace_schema_metadata(None)
+    assert a.equals(b.cast(a.schema))
+
+
 def test_cli_two_gpus_matches_one(data_dir, tmp_path):
     """Self-spawned multi-GPU run (one worker per GPU, NCCL gather) writes the same files as the single-GPU run."""
     if torch.cuda.device_count() < 2:
