@@ -22,6 +22,11 @@ __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 __device__ __forceinline__ float2 mul_negi(float2 a) { return make_float2(a.y, -a.x); }  // a * (-i)
 
+// Shared-memory FFT buffers are indexed through sidx(): one float2 of padding after every 16 keeps the radix-4
+// stages' strided stores (stride 4 and 16 complex = 32 / 128 bytes) off the same banks (8-way conflicts otherwise).
+__device__ __forceinline__ int sidx(int i) { return i + (i >> 4); }
+constexpr int spad(int n) { return n + (n >> 4) + 1; }
+
 // One Stockham stage of radix R over a length-N transform whose previous radices multiply to s.
 //   y[q + s*(R*p + k)] = w^(k) * sum_j x[q + s*(p + m*j)] * exp(-2 pi i jk/R),  w = exp(-2 pi i p s / N)
 // NT cooperating threads: 32 = one warp (__syncwarp between stages), otherwise the whole block (__syncthreads).
@@ -35,7 +40,7 @@ __device__ __forceinline__ void fft_stage(const float2* __restrict__ x, float2* 
     const int p = i / s;
     float2 a[R];
 #pragma unroll
-    for (int j = 0; j < R; ++j) a[j] = x[i + NB * j];
+    for (int j = 0; j < R; ++j) a[j] = x[sidx(i + NB * j)];
     float2 b[R];
     if (R == 2) {
       b[0] = cadd(a[0], a[1]);
@@ -68,9 +73,9 @@ __device__ __forceinline__ void fft_stage(const float2* __restrict__ x, float2* 
     }
     const int base = q + s * R * p;
     const int step = p * s;  // twiddle index of w
-    y[base] = b[0];
+    y[sidx(base)] = b[0];
 #pragma unroll
-    for (int k = 1; k < R; ++k) y[base + s * k] = (m == 1) ? b[k] : cmul(b[k], tw[(step * k) % N]);
+    for (int k = 1; k < R; ++k) y[sidx(base + s * k)] = (m == 1) ? b[k] : cmul(b[k], tw[(step * k) % N]);
   }
   if (NT == 32) __syncwarp(); else __syncthreads();
 }
@@ -142,7 +147,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fbank_kernel(const void* 
                                                                     int total_frames, const float* __restrict__ window,
                                                                     const float2* __restrict__ tw, MelTable mt,
                                                                     float* __restrict__ feat) {
-  __shared__ float2 sbuf[kWarpsPerBlock][2][512];
+  __shared__ float2 sbuf[kWarpsPerBlock][2][spad(512)];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float2* A = sbuf[warp][0];
   float2* B = sbuf[warp][1];
@@ -166,7 +171,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fbank_kernel(const void* 
   for (int i = lane; i < 400; i += 32) {
     const float x0 = valid[0] ? load_pcm<S16>(pcm, start[0] + i) : 0.f;
     const float x1 = valid[1] ? load_pcm<S16>(pcm, start[1] + i) : 0.f;
-    B[i] = make_float2(x0, x1);
+    B[sidx(i)] = make_float2(x0, x1);
     s0 += x0;
     s1 += x1;
   }
@@ -177,20 +182,20 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fbank_kernel(const void* 
   for (int i = lane; i < 512; i += 32) {
     float2 v = make_float2(0.f, 0.f);
     if (i < 400) {
-      const float2 c = B[i];
-      const float2 p = B[i > 0 ? i - 1 : 0];
+      const float2 c = B[sidx(i)];
+      const float2 p = B[sidx(i > 0 ? i - 1 : 0)];
       const float w = __ldg(window + i);
       v.x = ((c.x - m0) - 0.97f * (p.x - m0)) * w;
       v.y = ((c.y - m1) - 0.97f * (p.y - m1)) * w;
     }
-    A[i] = v;
+    A[sidx(i)] = v;
   }
   __syncwarp();
   float2* Z = fft512(A, B, tw, lane);
   float* P = reinterpret_cast<float*>(Z == A ? B : A);  // power spectra: P[k] frame 0, P[257 + k] frame 1
   for (int k = lane; k <= 256; k += 32) {
-    const float2 z = Z[k];
-    const float2 zc = Z[(512 - k) & 511];
+    const float2 z = Z[sidx(k)];
+    const float2 zc = Z[sidx((512 - k) & 511)];
     const float ar = 0.5f * (z.x + zc.x), ai = 0.5f * (z.y - zc.y);   // frame 0 spectrum
     const float br = 0.5f * (z.y + zc.y), bi = -0.5f * (z.x - zc.x);  // frame 1 spectrum
     P[k] = ar * ar + ai * ai;
@@ -247,7 +252,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) logmel_kernel(const void*
                                                                      int total_frames, const float* __restrict__ window,
                                                                      const float2* __restrict__ tw, MelTable mt,
                                                                      float* __restrict__ raw, int* __restrict__ umax) {
-  __shared__ float2 sbuf[kWarpsPerBlock][2][400];
+  __shared__ float2 sbuf[kWarpsPerBlock][2][spad(400)];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float2* A = sbuf[warp][0];
   float2* B = sbuf[warp][1];
@@ -282,14 +287,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) logmel_kernel(const void*
         if (f == 0) v.x = x; else v.y = x;
       }
     }
-    A[i] = v;
+    A[sidx(i)] = v;
   }
   __syncwarp();
   float2* Z = fft400(A, B, tw, lane);
   float* P = reinterpret_cast<float*>(Z == A ? B : A);
   for (int k = lane; k <= 200; k += 32) {
-    const float2 z = Z[k];
-    const float2 zc = Z[k == 0 ? 0 : 400 - k];
+    const float2 z = Z[sidx(k)];
+    const float2 zc = Z[sidx(k == 0 ? 0 : 400 - k)];
     const float ar = 0.5f * (z.x + zc.x), ai = 0.5f * (z.y - zc.y);
     const float br = 0.5f * (z.y + zc.y), bi = -0.5f * (z.x - zc.x);
     P[k] = ar * ar + ai * ai;
@@ -364,8 +369,8 @@ __global__ void __launch_bounds__(kMmThreads) matcha_mel_kernel(const void* __re
                                                                 int total_frames, const float* __restrict__ window,
                                                                 const float2* __restrict__ tw, MelTable mt,
                                                                 float* __restrict__ out) {
-  __shared__ float2 A[kMmN];
-  __shared__ float2 B[kMmN];
+  __shared__ float2 A[spad(kMmN)];
+  __shared__ float2 B[spad(kMmN)];
   const int tid = threadIdx.x;
   const int slot = blockIdx.x;
   if (slot >= ((total_frames + n_utts) >> 1)) return;
@@ -391,7 +396,7 @@ __global__ void __launch_bounds__(kMmThreads) matcha_mel_kernel(const void* __re
         if (f == 0) v.x = x; else v.y = x;
       }
     }
-    A[i] = v;
+    A[sidx(i)] = v;
   }
   __syncthreads();
   fft_stage<kMmN, 4, kMmThreads>(A, B, 1, tw, tid);
@@ -402,8 +407,8 @@ __global__ void __launch_bounds__(kMmThreads) matcha_mel_kernel(const void* __re
   fft_stage<kMmN, 2, kMmThreads>(B, A, 960, tw, tid);
   float* P = reinterpret_cast<float*>(B);   // magnitudes: P[k] frame 0, P[961 + k] frame 1
   for (int k = tid; k < kMmBins; k += kMmThreads) {
-    const float2 z = A[k];
-    const float2 zc = A[k == 0 ? 0 : kMmN - k];
+    const float2 z = A[sidx(k)];
+    const float2 zc = A[sidx(k == 0 ? 0 : kMmN - k)];
     const float ar = 0.5f * (z.x + zc.x), ai = 0.5f * (z.y - zc.y);
     const float br = 0.5f * (z.y + zc.y), bi = -0.5f * (z.x - zc.x);
     P[k] = sqrtf(ar * ar + ai * ai + 1e-9f);

@@ -16,6 +16,7 @@ from .engine import Engine, kaldi_num_frames, token_len, whisper_num_frames
 
 SR = 16000
 MAX_TOKEN_SECONDS = 30  # tools/extract_speech_token.py:34: strictly longer than 30 s -> []
+RAMP_UTTS = 48          # Extractor.extract: size of the first (ramp-up) batch
 
 
 @dataclass
@@ -61,6 +62,8 @@ class Extractor:
         self.max_batch_utts = max_batch_utts
         self._pin = None
         self._copy_stream = None
+        self._d2h_stream = None
+        self._res = [(None, None), (None, None)]
 
     # ------------------------------------------------------------------ device-side preparation
     def _to_device_16k(self, utts: Sequence[Utt], mono: str):
@@ -138,23 +141,41 @@ class Extractor:
             return self.embed(utts), self.tokenize(utts)
         dur = [u.samples.shape[0] / SR for u in utts]
         batches = plan_batches(dur, self.max_batch_seconds, self.max_batch_utts)
+        if len(batches[0]) > 2 * RAMP_UTTS:      # short ramp-up batch: the GPU starts after staging 48 clips, not 1,000
+            batches[0:1] = [batches[0][:RAMP_UTTS], batches[0][RAMP_UTTS:]]
         total = sum(u.samples.shape[0] for u in utts)
         if self._pin is None or self._pin.numel() < total:
             self._pin = torch.empty(max(total, 1), dtype=torch.int16).pin_memory()
         host = self._pin.numpy()
+        dev = self.eng.device
+        main = torch.cuda.current_stream(dev)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(dev)
+            self._d2h_stream = torch.cuda.Stream(dev)
+        out = np.zeros((len(utts), 192), dtype=np.float32)
+        toks: List[List[int]] = [[] for _ in utts]
+
+        def finish(item):
+            """Host side of one batch: wait for its device-to-host copies, then unpack (runs under later batches)."""
+            idx, counts, emb_h, tok_h, done = item
+            done.synchronize()
+            out[idx] = emb_h.numpy()
+            th = tok_h.numpy()
+            p = 0
+            for i, n in zip(idx, counts):
+                toks[i] = th[p:p + n].tolist()
+                p += n
+
         pending, o = [], 0
-        for idx in batches:
+        for k, idx in enumerate(batches):
             lens = [utts[i].samples.shape[0] for i in idx]
             b0 = o
             for i, n in zip(idx, lens):
                 host[o:o + n] = utts[i].samples[:, 0]
                 o += n
             # upload on a side stream: the copy of batch k+1 runs under the kernels of batch k
-            main = torch.cuda.current_stream(self.eng.device)
-            if self._copy_stream is None:
-                self._copy_stream = torch.cuda.Stream(self.eng.device)
             with torch.cuda.stream(self._copy_stream):
-                pcm = self._pin[b0:o].to(self.eng.device, non_blocking=True)
+                pcm = self._pin[b0:o].to(dev, non_blocking=True)
                 ready = torch.cuda.Event()
                 ready.record(self._copy_stream)
             main.wait_event(ready)
@@ -163,17 +184,34 @@ class Extractor:
             emb = self.eng.campplus(feat, frames)
             mel, mframes = self.eng.logmel(pcm, lens)
             tok, counts = self.eng.s3tok(mel, mframes)
-            pending.append((idx, emb, tok, counts))
-        out = np.zeros((len(utts), 192), dtype=np.float32)
-        toks: List[List[int]] = [[] for _ in utts]
-        for idx, emb, tok, counts in pending:
-            out[idx] = emb.cpu().numpy()
-            th = tok.cpu().numpy()
-            p = 0
-            for i, n in zip(idx, counts):
-                toks[i] = th[p:p + n].tolist()
-                p += n
+            computed = torch.cuda.Event()
+            computed.record(main)
+            # results leave on a third stream into pinned buffers (two alternating sets), unpacked one batch later
+            emb_h, tok_h = self._result_buffers(k & 1, emb.shape[0], tok.numel())
+            with torch.cuda.stream(self._d2h_stream):
+                self._d2h_stream.wait_event(computed)
+                emb_h.copy_(emb, non_blocking=True)
+                tok_h.copy_(tok, non_blocking=True)
+                done = torch.cuda.Event()
+                done.record(self._d2h_stream)
+            emb.record_stream(self._d2h_stream)
+            tok.record_stream(self._d2h_stream)
+            pending.append((idx, counts, emb_h, tok_h, done))
+            if len(pending) == 2:
+                finish(pending.pop(0))
+        for item in pending:
+            finish(item)
         return out, toks
+
+    def _result_buffers(self, slot: int, n_emb: int, n_tok: int):
+        """Pinned host buffers for one batch's results (grown on demand, reused across calls)."""
+        e, t = self._res[slot]
+        if e is None or e.shape[0] < n_emb:
+            e = torch.empty((max(n_emb, 256), 192), dtype=torch.float32).pin_memory()
+        if t is None or t.numel() < n_tok:
+            t = torch.empty(max(n_tok, 4096), dtype=torch.int32).pin_memory()
+        self._res[slot] = (e, t)
+        return e[:n_emb], t[:n_tok]
 
     # ------------------------------------------------------------------ stage 2
     def tokenize_batch(self, utts: Sequence[Utt]):

@@ -45,3 +45,22 @@ def test_results_do_not_depend_on_batch_composition(engine):
             assert torch.equal(part[5][t:t + nt], full[5][to[i]:to[i + 1]])                      # token ids
             assert torch.equal(part[6][t:t + nt], full[6][to[i]:to[i + 1]])                      # pre-FSQ values
             f, m, t = f + nf, m + nm, t + nt
+
+
+def test_extract_equals_single_stage_paths(engine):
+    """Extractor.extract (one upload per batch, ramp-up batch, asynchronous result read-back over three streams) must
+    return exactly what embed() + tokenize() return, in the caller's order, across repeated calls."""
+    from fangyan_tts_b200 import synth_weights
+    from fangyan_tts_b200.configs import CamPlusConfig, S3Config
+    from fangyan_tts_b200.pipeline import Extractor, Utt
+    cfg = S3Config(n_layer=2)
+    engine.load_campplus(synth_weights.campplus_state(seed=21), CamPlusConfig())
+    engine.load_s3tok(synth_weights.s3tok_state(cfg, seed=22), cfg)
+    rng = np.random.default_rng(99)
+    utts = [Utt(synth.utterance(rng, float(rng.uniform(0.5, 6.0)))[:, None]) for _ in range(150)]
+    ex = Extractor(engine, max_batch_seconds=120.0, max_batch_utts=128)        # several batches + the ramp-up split
+    emb_ref, tok_ref = ex.embed(utts), ex.tokenize(utts)
+    for _ in range(2):
+        emb, toks = ex.extract(utts)
+        assert np.array_equal(emb, emb_ref)
+        assert toks == tok_ref
