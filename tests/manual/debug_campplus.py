@@ -7,7 +7,7 @@ import numpy as np
 import torch
 import torch.nn.functional as Fn
 
-sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent.parent))
 from fangyan_tts_b200 import synth
 from fangyan_tts_b200.engine import Engine
 from oracle import campplus as CP

@@ -8,7 +8,8 @@ import torch
 
 import bench
 from fangyan_tts_b200.engine import Engine
-from oracle import campplus as CP, s3tokenizer as S3
+from fangyan_tts_b200 import synth_weights
+from fangyan_tts_b200.configs import CamPlusConfig, S3Config
 
 
 def main():
@@ -16,12 +17,9 @@ def main():
     prec = sys.argv[2] if len(sys.argv) > 2 else "bf16x3"
     steps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
     eng = Engine(0, prec)
-    cam_cfg, s3_cfg = CP.CamPlusConfig(), S3.S3Config()
-    eng.load_campplus(dict(CP.init_random(CP.CamPlus(cam_cfg)).state_dict()), cam_cfg)
-    s3 = S3.init_random(S3.S3Tokenizer(s3_cfg))
-    st = dict(s3.state_dict())
-    st["rope.cos"], st["rope.sin"] = S3.rope_tables(2048, s3_cfg.d_head, s3_cfg.rope_theta)
-    eng.load_s3tok(st, s3_cfg)
+    cam_cfg, s3_cfg = CamPlusConfig(), S3Config()
+    eng.load_campplus(synth_weights.campplus_state(), cam_cfg)          # product-side random-init weights
+    eng.load_s3tok(synth_weights.s3tok_state(s3_cfg), s3_cfg)
     utts = bench.workload(n, 1988)
     lens = [len(u) for u in utts]
     pcm = torch.from_numpy(np.concatenate(utts)).cuda()
