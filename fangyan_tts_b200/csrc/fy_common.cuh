@@ -44,6 +44,12 @@ struct GemmSeg {
   int a_col;      // first K column in A
   int b_col;      // first K column in B
   int nkb;        // number of 64-wide K blocks
+  // Fused split-bf16 segment (a_lo != 0): per K block the operands A_hi, A_lo, B_hi, B_lo are loaded ONCE into two
+  // consecutive ring slots ((A_hi, B_hi), (A_lo, B_lo)) and feed three products hi*hi + hi*lo + lo*hi, instead of
+  // three separate segments that fetch six tiles.  a_lo / b_lo = column distance from the hi to the lo half.
+  // A GEMM uses either fused segments only or none (ring-slot parity), and only kernels with an even ring depth.
+  int a_lo = 0;
+  int b_lo = 0;
 };
 
 // EPI_QKV_ROPE: the fused q|k|v projection of the S3 encoder.  Column block n0 / rope_D selects q, k or v; q and k get

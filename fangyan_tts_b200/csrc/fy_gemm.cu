@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
   const int num_tiles = num_m * num_n;
 #ifdef FY_STALLPROF
   int sp_kb = 0;
-  for (int s = 0; s < args.nseg; ++s) sp_kb += args.seg[s].nkb;
+  for (int s = 0; s < args.nseg; ++s) sp_kb += args.seg[s].nkb * (args.seg[s].a_lo ? 3 : 1);
   const int sp_slot = 8 * (args.N == 3840 ? 0 : args.N == 5120 ? 1 : (args.N == 1280 && sp_kb == 60) ? 2
                                                                       : (args.N == 1280 && sp_kb == 240) ? 3 : 4);
 #endif
@@ -192,7 +192,11 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
         const int n0 = (tile % num_n) * BN + (int)cta_rank * (BN / NCTA);   // pair: this CTA's half of the B tile
         for (int s = 0; s < args.nseg; ++s) {
           const GemmSeg sg = args.seg[s];
-          for (int kb = 0; kb < sg.nkb; ++kb) {
+          const int nparts = sg.a_lo ? 2 : 1;   // fused split segment: (A_hi, B_hi) then (A_lo, B_lo) per K block
+          for (int kbp = 0; kbp < sg.nkb * nparts; ++kbp) {
+            const int kb = sg.a_lo ? kbp >> 1 : kbp;
+            const int a_c = sg.a_col + ((sg.a_lo && (kbp & 1)) ? sg.a_lo : 0) + kb * BKE;
+            const int b_c = sg.b_col + ((sg.a_lo && (kbp & 1)) ? sg.b_lo : 0) + kb * BKE;
             FY_SP(const long long sp_a = clock64();)
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
             FY_SP(sp_wait += clock64() - sp_a;)
@@ -203,14 +207,14 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
               // complete until this (the only) arrival, and the peer cannot run a ring revolution ahead because its
               // empty barrier is only released by the leader's MMA commit.
               if (cta_rank == 0) ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes * 2);
-              ptx::tma_load_2d_pair(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
-              ptx::tma_load_2d_pair(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
+              ptx::tma_load_2d_pair(a_dst, &args.tmap_a, &full_bar[stage], a_c, m0 + sg.a_row_off);
+              ptx::tma_load_2d_pair(b_dst, &args.tmap_b, &full_bar[stage], b_c, n0);
             } else {
               ptx::mbar_expect_tx(&full_bar[stage], C::kStageBytes);
-              ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], sg.a_col + kb * BKE, m0 + sg.a_row_off);
-              ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0);
+              ptx::tma_load_2d(a_dst, &args.tmap_a, &full_bar[stage], a_c, m0 + sg.a_row_off);
+              ptx::tma_load_2d(b_dst, &args.tmap_b, &full_bar[stage], b_c, n0);
               if (BN == 256)   // tensor-map boxes are at most 128 rows (shared with the pair kernel): second half
-                ptx::tma_load_2d(b_dst + 128 * 128, &args.tmap_b, &full_bar[stage], sg.b_col + kb * BKE, n0 + 128);
+                ptx::tma_load_2d(b_dst + 128 * 128, &args.tmap_b, &full_bar[stage], b_c, n0 + 128);
             }
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
           }
@@ -238,6 +242,36 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
         uint32_t accumulate = 0;
         for (int s = 0; s < args.nseg; ++s) {
           const int nkb = args.seg[s].nkb;
+          if (args.seg[s].a_lo) {
+            // fused split: slots (stage, stage + 1) hold (A_hi, B_hi) and (A_lo, B_lo); the ring depth is even and
+            // every segment of the GEMM is fused, so stage is even here and the pair never wraps
+            for (int kb = 0; kb < nkb; ++kb) {
+              FY_SP(const long long sp_b = clock64();)
+              ptx::mbar_wait(&full_bar[stage], phase);
+              ptx::mbar_wait(&full_bar[stage + 1], phase);
+              FY_SP(sp_wf += clock64() - sp_b;)
+              ptx::tc_fence_after();
+              const uint32_t s0 = ptx::smem_u32(tiles + stage * C::kStageBytes);
+              const uint32_t s1 = s0 + C::kStageBytes;
+              const uint64_t a_hi = ptx::make_desc_sw128(s0), b_hi = ptx::make_desc_sw128(s0 + C::kABytes);
+              const uint64_t a_lo = ptx::make_desc_sw128(s1), b_lo = ptx::make_desc_sw128(s1 + C::kABytes);
+#pragma unroll
+              for (int pr = 0; pr < 3; ++pr) {
+                const uint64_t da = pr == 2 ? a_lo : a_hi, db = pr == 1 ? b_lo : b_hi;
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  if (PAIR) ptx::mma_bf16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+                  else ptx::mma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+                  accumulate = 1;
+                }
+              }
+              if (PAIR) { ptx::mma_commit_pair(&empty_bar[stage]); ptx::mma_commit_pair(&empty_bar[stage + 1]); }
+              else { ptx::mma_commit(&empty_bar[stage]); ptx::mma_commit(&empty_bar[stage + 1]); }
+              stage += 2;
+              if (stage == C::kStages) { stage = 0; phase ^= 1; }
+            }
+            continue;
+          }
           for (int kb = 0; kb < nkb; ++kb) {
             FY_SP(const long long sp_b = clock64();)
             ptx::mbar_wait(&full_bar[stage], phase);
@@ -718,6 +752,10 @@ int gemm_block_n(int N) {
 int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t st) {
   FY_CHECK(a.M > 0 && a.nseg > 0 && a.nseg <= kMaxSeg, FY_ERR_ARG, "bad GEMM shape M=%d nseg=%d", a.M, a.nseg);
   FY_CHECK(a.epi.out != nullptr && a.epi.ldo > 0, FY_ERR_ARG, "GEMM epilogue has no output");
+  int n_fused = 0;
+  for (int i = 0; i < a.nseg; ++i) n_fused += a.seg[i].a_lo != 0;
+  FY_CHECK(n_fused == 0 || (n_fused == a.nseg && a.op == OP_BF16 && gemm_block_n(a.N) == 256), FY_ERR_ARG,
+           "fused split segments need every segment fused, bf16 operands and a 256-wide tile (N=%d)", a.N);
   switch (gemm_block_n(a.N)) {
 #define FY_DISPATCH_OP(BN_)                                                          \
   switch (a.op) {                                                                    \

@@ -98,8 +98,15 @@ std::vector<float> conv_tap_major(const float* w, int64_t co, int64_t ci, int64_
 
 // Three-product segment list for a K-range: hi*hi (+ hi*lo + lo*hi when split).
 // a_col/b_col address the hi halves; lo halves sit a_lo / b_lo columns further.
+// With a 256-wide tile (g.N set before the call, a multiple of 256) the split is one FUSED segment: each K block's
+// four operand tiles are fetched once for the three products (FY_GEMM_FUSED_SPLIT=0 restores three segments).
 void add_products(GemmArgs& g, int W, int a_row_off, int a_col, int b_col, int K, int a_lo, int b_lo) {
   const int nkb = K / 64;
+  static const bool fused_ok = [] { const char* e = getenv("FY_GEMM_FUSED_SPLIT"); return !(e && e[0] == '0'); }();
+  if (W == 2 && fused_ok && g.N > 0 && gemm_block_n(g.N) == 256) {
+    g.seg[g.nseg++] = GemmSeg{a_row_off, a_col, b_col, nkb, a_lo, b_lo};
+    return;
+  }
   g.seg[g.nseg++] = GemmSeg{a_row_off, a_col, b_col, nkb};
   if (W == 2) {
     g.seg[g.nseg++] = GemmSeg{a_row_off, a_col, b_col + b_lo, nkb};
