@@ -41,6 +41,34 @@ __device__ __forceinline__ uint32_t tile_addr(uint32_t base, int row, int chunk)
   return base + row * 128 + ((chunk ^ (row & 7)) << 4);
 }
 
+// Per-thread constants of load_tile's access pattern: thread t moves chunk (t & 7) of rows (t >> 3) + 16 i, i < 4.
+// With them a tile load is four cp.async whose addresses are base + i * stride (no per-call index arithmetic).
+struct TileLane {
+  uint32_t soff;      // byte offset of (row r0, chunk ch) inside a swizzled tile
+  int r0;             // first row of this thread
+  size_t goff;        // element offset r0 * ld + ch * 8 inside the global tile
+  size_t gstep;       // 16 * ld elements
+};
+__device__ __forceinline__ TileLane tile_lane(int tid, int ld) {
+  TileLane t;
+  t.r0 = tid >> 3;
+  const int ch = tid & 7;
+  t.soff = t.r0 * 128 + ((ch ^ (t.r0 & 7)) << 4);     // (r0 + 16 i) & 7 == r0 & 7
+  t.goff = (size_t)t.r0 * ld + ch * 8;
+  t.gstep = (size_t)16 * ld;
+  return t;
+}
+__device__ __forceinline__ void load_tile(uint32_t sbase, const __nv_bfloat16* g, const TileLane& t, int nvalid) {
+  const __nv_bfloat16* p = g + t.goff;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const bool ok = t.r0 + 16 * i < nvalid;
+    cp_async16(sbase + t.soff + i * 2048, p, ok);   // !ok: src-size 0, nothing is read (rows past the utterance are
+                                                    // still inside the caller's q/k/v workspace)
+    p += t.gstep;
+  }
+}
+
 // Load a [64][64] bf16 tile: global rows row0.. (stride ld elements), zero-filled for rows >= nvalid.
 __device__ __forceinline__ void load_tile(uint32_t sbase, const __nv_bfloat16* g, size_t ld, int nvalid, int tid) {
 #pragma unroll
@@ -61,6 +89,10 @@ __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+// bf16 pair of the residuals (a - hi(a), b - hi(b)) given the already packed pair hi = (bf16(a), bf16(b))
+__device__ __forceinline__ uint32_t pack_lo(uint32_t hi, float a, float b) {
+  return pack2(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xffff0000u));
 }
 __device__ __forceinline__ float bf_round(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
 
@@ -90,12 +122,16 @@ __global__ void __launch_bounds__(kThreads, 3) attention_kernel(const __nv_bfloa
   const int nkt = (L + kBK - 1) / kBK;
 
   // prologue: Q and first K/V tile
+  const TileLane tlane = tile_lane(tid, ld);
+  const __nv_bfloat16* kp = k + (size_t)P * ld + col;    // this (utterance, head)'s key / value rows, advanced per tile
+  const __nv_bfloat16* vp = v + (size_t)P * ld + col;
+  const size_t tile_step = (size_t)kBK * ld;
 #pragma unroll
-  for (int p = 0; p < NP; ++p) load_tile(sQ + p * TILE, q + (size_t)(P + q0) * ld + col + p * lo_off, ld, nq, tid);
+  for (int p = 0; p < NP; ++p) load_tile(sQ + p * TILE, q + (size_t)(P + q0) * ld + col + p * lo_off, tlane, nq);
 #pragma unroll
   for (int p = 0; p < NP; ++p) {
-    load_tile(sKV + p * TILE, k + (size_t)P * ld + col + p * lo_off, ld, min(kBK, L), tid);
-    load_tile(sKV + (NP + p) * TILE, v + (size_t)P * ld + col + p * lo_off, ld, min(kBK, L), tid);
+    load_tile(sKV + p * TILE, kp + p * lo_off, tlane, min(kBK, L));
+    load_tile(sKV + (NP + p) * TILE, vp + p * lo_off, tlane, min(kBK, L));
   }
   cp_commit();
 
@@ -124,10 +160,12 @@ __global__ void __launch_bounds__(kThreads, 3) attention_kernel(const __nv_bfloa
     if (kt + 1 < nkt) {
       const int k0n = (kt + 1) * kBK;
       const uint32_t sb = sKV + (st ^ 1) * 2 * NP * TILE;
+      kp += tile_step;
+      vp += tile_step;
 #pragma unroll
       for (int p = 0; p < NP; ++p) {
-        load_tile(sb + p * TILE, k + (size_t)(P + k0n) * ld + col + p * lo_off, ld, min(kBK, L - k0n), tid);
-        load_tile(sb + (NP + p) * TILE, v + (size_t)(P + k0n) * ld + col + p * lo_off, ld, min(kBK, L - k0n), tid);
+        load_tile(sb + p * TILE, kp + p * lo_off, tlane, min(kBK, L - k0n));
+        load_tile(sb + (NP + p) * TILE, vp + p * lo_off, tlane, min(kBK, L - k0n));
       }
       cp_commit();
     }
@@ -227,11 +265,11 @@ __global__ void __launch_bounds__(kThreads, 3) attention_kernel(const __nv_bfloa
       pa[0][1] = pack2(s[2 * ks][2], s[2 * ks][3]);
       pa[0][2] = pack2(s[2 * ks + 1][0], s[2 * ks + 1][1]);
       pa[0][3] = pack2(s[2 * ks + 1][2], s[2 * ks + 1][3]);
-      if (SPLIT) {
-        pa[NP - 1][0] = pack2(s[2 * ks][0] - bf_round(s[2 * ks][0]), s[2 * ks][1] - bf_round(s[2 * ks][1]));
-        pa[NP - 1][1] = pack2(s[2 * ks][2] - bf_round(s[2 * ks][2]), s[2 * ks][3] - bf_round(s[2 * ks][3]));
-        pa[NP - 1][2] = pack2(s[2 * ks + 1][0] - bf_round(s[2 * ks + 1][0]), s[2 * ks + 1][1] - bf_round(s[2 * ks + 1][1]));
-        pa[NP - 1][3] = pack2(s[2 * ks + 1][2] - bf_round(s[2 * ks + 1][2]), s[2 * ks + 1][3] - bf_round(s[2 * ks + 1][3]));
+      if (SPLIT) {   // lo = p - hi, with hi read back from the packed pair (one shift / one mask per element)
+        pa[NP - 1][0] = pack_lo(pa[0][0], s[2 * ks][0], s[2 * ks][1]);
+        pa[NP - 1][1] = pack_lo(pa[0][1], s[2 * ks][2], s[2 * ks][3]);
+        pa[NP - 1][2] = pack_lo(pa[0][2], s[2 * ks + 1][0], s[2 * ks + 1][1]);
+        pa[NP - 1][3] = pack_lo(pa[0][3], s[2 * ks + 1][2], s[2 * ks + 1][3]);
       }
 #pragma unroll
       for (int jpg = 0; jpg < 2; ++jpg) {  // two pairs of 8-wide d tiles = four independent accumulators
