@@ -17,7 +17,7 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 __device__ __forceinline__ float2 unpack2(uint32_t u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
 
 // Stem: Conv2d(1, 32, 3x3, pad 1) + BN + ReLU over (freq, time).  feat is packed [frames, 80] fp32.
-// out: [R100, 82, 32] fp16 channels-last with zero columns at p = 0 and p = 81 (buffer pre-zeroed).
+// out: [R100, 82, 32] fp16 channels-last with zero columns at p = 0 and p = 81 (zero_pads_kernel) and zero guard rows.
 // rowsrc[r] = feat row of time row r or -1 for guard rows.  w: [32][3 (freq)][3 (time)].
 // grid = R100, block = 320 (80 freq x 4 groups of 8 channels).
 __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ feat, const int* __restrict__ rowsrc,
@@ -26,7 +26,11 @@ __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ fea
                                                    __half* __restrict__ out) {
   const int r = blockIdx.x;
   const int src = rowsrc[r];
-  if (src < 0) return;
+  if (src < 0) {   // guard row: explicit zeros (the workspace is not cleared; the pad slots come from zero_pads_kernel)
+    *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + threadIdx.x % 80 + 1) * 32 + (threadIdx.x / 80) * 8) =
+        make_uint4(0u, 0u, 0u, 0u);
+    return;
+  }
   __shared__ float in[3][82];
   __shared__ float sw[32 * 9 + 64];
   for (int i = threadIdx.x; i < 32 * 9; i += 320) sw[i] = w[i];
@@ -58,6 +62,34 @@ __global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ fea
   uint4 o;
   o.x = pack2(y[0], y[1]); o.y = pack2(y[2], y[3]); o.z = pack2(y[4], y[5]); o.w = pack2(y[6], y[7]);
   *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8) = o;
+}
+
+// The FCM activation buffers [R100][fp slots][32 ch] fp16 keep one zero pad slot at each end of every time row (the
+// frequency padding of the 3x3 convolutions) plus 64 bytes after the last row (second half of the last overlapping
+// view row).  The convolution epilogues never write those, and the workspace is reused across calls and stages, so
+// they are cleared here -- 128 bytes per row instead of a memset of every buffer (3.5 GB at 250 utterances).
+struct PadBufs {
+  __half* ptr[9];
+  int fp[9];
+  int n;
+};
+__global__ void __launch_bounds__(256) zero_pads_kernel(PadBufs b, int R100) {
+  const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+  const size_t per_buf = (size_t)(R100 + 1) * 8;        // 8 x 16 bytes per row, one extra "row" for the tail
+  if (idx >= per_buf * b.n) return;
+  const int buf = (int)(idx / per_buf);
+  const size_t rem = idx % per_buf;
+  const int r = (int)(rem >> 3), k = (int)(rem & 7);
+  char* base = reinterpret_cast<char*>(b.ptr[buf]);
+  const size_t row_bytes = (size_t)b.fp[buf] * 64;
+  char* dst;
+  if (r == R100) {
+    if (k >= 4) return;
+    dst = base + (size_t)R100 * row_bytes + k * 16;                                  // the 64-byte tail
+  } else {
+    dst = base + (size_t)r * row_bytes + (k < 4 ? 0 : row_bytes - 64) + (k & 3) * 16;  // first / last slot of row r
+  }
+  *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
 }
 
 // mask[g] = -2 (skip) when slot g % Q is outside [lo, hi]; else -1 (write zero) on guard time rows; else 0

@@ -395,8 +395,17 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   auto Fp = [&](size_t off) { return reinterpret_cast<float*>(base + off); };
   auto H = [&](size_t off) { return reinterpret_cast<__half*>(base + off); };
   int *m42s = I(lay.o_m42s), *m42 = I(lay.o_m42), *m22s = I(lay.o_m22s), *m22 = I(lay.o_m22), *m11s = I(lay.o_m11s);
-  // zero the FCM activation buffers (pads and guard rows must read as zero) -- one contiguous span
-  FY_CUDA(cudaMemsetAsync(base + lay.o_x0, 0, lay.o_fcm - lay.o_x0, st));
+  // pad slots and tails of the FCM activation buffers must read as zero (guard rows are written by the stem / the
+  // convolution epilogues): cleared explicitly, see zero_pads_kernel
+  {
+    camk::PadBufs pb;
+    const size_t offs[9] = {lay.o_x0, lay.o_y40, lay.o_s40, lay.o_z40a, lay.o_z40b, lay.o_y20, lay.o_s20, lay.o_z20a, lay.o_z20b};
+    const int fps[9] = {82, 42, 42, 42, 42, 22, 22, 22, 22};
+    pb.n = 9;
+    for (int i = 0; i < 9; ++i) { pb.ptr[i] = H(offs[i]); pb.fp[i] = fps[i]; }
+    const size_t n = (size_t)(R100 + 1) * 8 * pb.n;
+    camk::zero_pads_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(pb, R100);
+  }
   {
     auto mk = [&](int Q, int lo, int hi, int* m) {
       const int n = R100 * Q;

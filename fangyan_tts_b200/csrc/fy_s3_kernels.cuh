@@ -18,7 +18,8 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // mel (reference layout [128][T_u] per utterance, fp32) -> time-major bf16 rows at row 4*P_u + 3 + t.
-// rows: [Rmel, 128 * W] with hi at [0,128) and (W == 2) lo at [128,256).  Buffer is zeroed beforehand.
+// rows: [Rmel, 128 * W] with hi at [0,128) and (W == 2) lo at [128,256).  Rows outside the utterances are cleared by
+// zero_gap_rows_kernel.
 // grid: (ceil(Tmax / 32), n_utts), block 256.
 template <bool SPLIT>
 __global__ void __launch_bounds__(256) mel_to_rows_kernel(const float* __restrict__ mel,
@@ -47,6 +48,22 @@ __global__ void __launch_bounds__(256) mel_to_rows_kernel(const float* __restric
       if (SPLIT) rows[(row0 + t) * LD + 128 + b] = lo;
     }
   }
+}
+
+// Zero every row of the mel operand buffer that is not an utterance's data: block b clears the rows between the data
+// of utterance b - 1 (or the start of the buffer) and the data of utterance b (or the end).  Those rows are the zero
+// padding of the stride-2 convolutions; clearing only them replaces a memset of the whole buffer.
+// grid: n_utts + 1, block 128; row_bytes is a multiple of 16.
+__global__ void __launch_bounds__(128) zero_gap_rows_kernel(__nv_bfloat16* __restrict__ rows, int row_bytes,
+                                                            const int* __restrict__ frame_off,
+                                                            const int* __restrict__ utt_P, int n_utts, int total_rows) {
+  const int b = blockIdx.x;
+  const int lo = b == 0 ? 0 : 4 * utt_P[b - 1] + 3 + (frame_off[b] - frame_off[b - 1]);
+  const int hi = b == n_utts ? total_rows : 4 * utt_P[b] + 3;
+  if (hi <= lo) return;
+  uint4* p = reinterpret_cast<uint4*>(reinterpret_cast<char*>(rows) + (size_t)lo * row_bytes);
+  const size_t n = (size_t)(hi - lo) * row_bytes / 16;
+  for (size_t i = threadIdx.x; i < n; i += 128) p[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 // LayerNorm over D (multiple of 128) per row: one warp per row.  out bf16 [rows, D * W] (hi | lo).

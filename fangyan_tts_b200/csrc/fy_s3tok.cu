@@ -382,7 +382,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   const int Rtok = lay.Rtok, R1 = lay.R1, Rmel = lay.Rmel;
 
   // ---- mel -> bf16 rows
-  FY_CUDA(cudaMemsetAsync(b_mel, 0, (size_t)Rmel * NM * W * 2, st));
+  s3k::zero_gap_rows_kernel<<<n_utts + 1, 128, 0, st>>>(b_mel, (int)(NM * W * 2), frame_off, d_P, n_utts, Rmel);
   {
     dim3 grid((Tmax + 31) / 32, n_utts);
     FY_CHECK(NM == 128, FY_ERR_ARG, "mel_to_rows supports n_mels == 128 only");
@@ -477,7 +477,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       FY_TRY(run_gemm(c, g, 2.0 * vtok * D * F));
     }
   }
-  c->launches += 3;  // memset, mel_to_rows, fsq
+  c->launches += 3;  // zero_gap_rows, mel_to_rows, fsq
   s3k::fsq_kernel<<<(Rtok + 7) / 8, 256, 0, st>>>(b_x, d_rutt, d_rpos, tok_off, p->pd_w, p->pd_b, Rtok, D, cf.fsq_scale,
                                                  tokens, fsq_pre);
   FY_CUDA(cudaGetLastError());

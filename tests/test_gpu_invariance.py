@@ -64,3 +64,28 @@ def test_extract_equals_single_stage_paths(engine):
         emb, toks = ex.extract(utts)
         assert np.array_equal(emb, emb_ref)
         assert toks == tok_ref
+
+
+def test_results_do_not_depend_on_workspace_contents(engine):
+    """The caller-owned workspace is never cleared wholesale: every byte a kernel reads must have been written in the
+    same call.  Poisoning it with 0xFF (NaN in fp16 / bf16 / fp32) between calls must not change a single bit."""
+    cfg = S3Config(n_layer=2)
+    engine.load_campplus(synth_weights.campplus_state(seed=11), CamPlusConfig())
+    engine.load_s3tok(synth_weights.s3tok_state(cfg, seed=12), cfg)
+    rng = np.random.default_rng(123)
+    utts = [synth.utterance(rng, float(rng.uniform(0.4, 5.0))) for _ in range(9)]
+    ref = _run(engine, utts, list(range(9)))
+    for fill in (0xFF, 0x7F):
+        engine._ws.fill_(fill)
+        got = _run(engine, utts, list(range(9)))
+        for a, b in zip(ref, got):
+            if torch.is_tensor(a):
+                assert torch.equal(a, b)
+            else:
+                assert a == b
+    # a different batch shape over the poisoned buffer (offsets of every sub-buffer move)
+    engine._ws.fill_(0xFF)
+    sub = _run(engine, utts, [1, 4, 7])
+    torch.cuda.synchronize()
+    one = _run(engine, utts, [4])
+    assert torch.equal(sub[4][1], one[4][0])                       # embedding of utterance 4
