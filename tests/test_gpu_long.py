@@ -52,3 +52,44 @@ def test_long_utterance_batch_256(engine):
         total += len(ids)
         bad += sum(a != b for a, b in zip(got, ids))
     assert bad / total <= 1e-3, (bad, total)
+
+
+def test_full_size_workload_properties(engine):
+    """BASELINE configs[1] at full size (the bench workload: 1,000 utterances of 3-10 s, all 12 encoder layers, CTA-pair
+    GEMMs with fused split segments), checked through size-independent properties: token counts bit-exact against the
+    length rule, ids inside the vocabulary, finite embeddings, bit-identical repeat, and -- for a sample -- the same
+    bits when the utterance is processed alone (the reference's batch-1 semantics) plus oracle parity."""
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+    import bench
+    from fangyan_tts_b200.pipeline import Extractor, Utt
+    cfg = S3Config()
+    cam_w, s3_w = synth_weights.campplus_state(), synth_weights.s3tok_state(cfg)
+    engine.load_campplus(cam_w, CamPlusConfig())
+    engine.load_s3tok(s3_w, cfg)
+    utts = bench.workload(1000, 1986)
+    ex = Extractor(engine, max_batch_seconds=2400.0)
+    emb, toks = ex.extract([Utt(u[:, None]) for u in utts])
+    assert emb.shape == (1000, 192) and np.isfinite(emb).all()
+    assert [len(t) for t in toks] == [token_len(len(u) // 160) for u in utts]
+    assert all(0 <= min(t) and max(t) < 6561 for t in toks)
+    emb2, toks2 = ex.extract([Utt(u[:, None]) for u in utts])
+    assert np.array_equal(emb, emb2) and toks == toks2
+    cam = CP.CamPlus()
+    cam.load_state_dict({k: torch.from_numpy(v) for k, v in cam_w.items()}, strict=False)
+    cam.eval()
+    s3 = S3.S3Tokenizer(S3.S3Config())
+    s3.load_state_dict({k: torch.from_numpy(v) for k, v in s3_w.items()})
+    s3.eval()
+    total = bad = 0
+    for i in (0, 333, 999):
+        e1, t1 = ex.extract([Utt(utts[i][:, None])])
+        assert np.array_equal(e1[0], emb[i]) and t1[0] == toks[i]
+        w = torch.from_numpy(utts[i].astype(np.float32) / 32768.0)[None]
+        ref = CP.embed_one(cam, F.cmn(F.kaldi_fbank(w)))
+        assert float(torch.nn.functional.cosine_similarity(torch.from_numpy(emb[i]), ref, dim=0)) >= 0.9999
+        ids = S3.tokenize_one(s3, F.whisper_log_mel(w))
+        total += len(ids)
+        bad += sum(a != b for a, b in zip(toks[i], ids))
+    assert bad / total <= 1e-3, (bad, total)
