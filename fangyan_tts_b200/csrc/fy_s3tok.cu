@@ -12,6 +12,7 @@
 #include <algorithm>
 
 #include "fy_attention.cuh"
+#include "fy_attention_tc.cuh"
 #include "fy_common.cuh"
 #include "fy_s3_kernels.cuh"
 
@@ -120,7 +121,7 @@ struct Layout {  // per-call sizes derived from the frame counts
   int n_utts = 0, Rtok = 0, R1 = 0, Rmel = 0, n_attn_tiles = 0, Tmax = 0;
   size_t o_meta, o_mel, o_c1, o_x, o_xn, o_q, o_k, o_v, o_att, o_h, total;
   // meta sub-offsets (ints)
-  size_t m_P, m_L, m_row1, m_rutt, m_rpos, m_tiles, meta_ints;
+  size_t m_P, m_L, m_row1, m_rutt, m_rpos, m_tiles, m_tiles128, meta_ints;
 };
 
 int token_len(int T) { const int l1 = (T - 1) / 2 + 1; return (l1 - 1) / 2 + 1; }
@@ -141,7 +142,8 @@ Layout make_layout(const fy_s3_config& c, int W, int n_utts, int rtok, int n_til
   l.m_rpos = l.m_rutt + rtok;
   l.m_tiles = l.m_rpos + rtok;
   l.m_tiles += l.m_tiles & 1;  // int2 alignment
-  l.meta_ints = l.m_tiles + 2 * (size_t)n_tiles;
+  l.m_tiles128 = l.m_tiles + 2 * (size_t)n_tiles;            // 128-row query tiles (tcgen05 attention), <= n_tiles
+  l.meta_ints = l.m_tiles128 + 2 * (size_t)n_tiles;
   size_t o = 0;
   l.o_meta = o; o = align_up(o + l.meta_ints * 4);
   l.o_mel = o; o = align_up(o + (size_t)l.Rmel * c.n_mels * W * 2);
@@ -360,6 +362,13 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
         ++ti;
       }
   }
+  int tiles128 = 0;
+  for (int u = 0; u < n_utts; ++u)
+    for (int q0 = 0; q0 < L[u]; q0 += 128) {
+      hm[lay.m_tiles128 + 2 * tiles128] = u;
+      hm[lay.m_tiles128 + 2 * tiles128 + 1] = q0;
+      ++tiles128;
+    }
   uint8_t* base = reinterpret_cast<uint8_t*>(ws);
   int* d_meta = reinterpret_cast<int*>(base + lay.o_meta);
   FY_CUDA(cudaMemcpyAsync(d_meta, hm, lay.meta_ints * 4, cudaMemcpyHostToDevice, st));
@@ -422,6 +431,24 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   FY_TRY(make_tmap_bf16(&m_att, b_att, Rtok, D * W, D * W, 128));
   FY_TRY(make_tmap_bf16(&m_h, b_h, Rtok, F * W, F * W, 128));
   FY_CHECK(D == 1280, FY_ERR_ARG, "layernorm kernel is instantiated for d_model == 1280 only (got %d)", D);
+  // tcgen05 attention (FY_ATTN_TC=1, split-bf16 only): TMA views of q, k, v and the 128-row tile list
+  static const bool attn_tc_env = [] { const char* e = getenv("FY_ATTN_TC"); return e && e[0] == '1'; }();
+  const bool attn_tc_on = attn_tc_env && W == 2 && cf.d_model / cf.n_head == 64 && cf.n_head % attn_tc::kHeadsPerCta == 0;
+  attn_tc::Params tc_params;
+  if (attn_tc_on) {
+    static bool configured = false;
+    if (!configured) {
+      FY_CUDA(cudaFuncSetAttribute(attn_tc::attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   attn_tc::kSmemBytes));
+      configured = true;
+    }
+    FY_TRY(make_tmap_bf16(&tc_params.tm_q, b_q, Rtok, D * W, D * W, 128));
+    FY_TRY(make_tmap_bf16(&tc_params.tm_kv, b_k, Rtok, D * W, D * W, 64));
+    FY_TRY(make_tmap_bf16(&tc_params.tm_v, b_v, Rtok, D * W, D * W, 64));
+    tc_params.out = b_att; tc_params.ld = D * W; tc_params.lo_off = D;
+    tc_params.tiles = reinterpret_cast<const int2*>(d_meta + lay.m_tiles128);
+    tc_params.utt_P = d_P; tc_params.utt_L = d_L;
+  }
   const float qk_scale = powf(64.0f, -0.25f);
   const int ln_grid = (Rtok + 7) / 8;
   for (int i = 0; i < cf.n_layer; ++i) {
@@ -443,7 +470,13 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       if (W == 2) s3k::fsmn_kernel<31, true><<<fg, 128, 0, st>>>(b_v, D * W, D, d_tiles, d_P, d_L, Lw.fsmn, D, b_x);
       else s3k::fsmn_kernel<31, false><<<fg, 128, 0, st>>>(b_v, D * W, D, d_tiles, d_P, d_L, Lw.fsmn, D, b_x);
     }
-    {
+    if (attn_tc_on) {
+      const int pi = prof_begin(c, PK_ATTN);
+      dim3 grid(tiles128, cf.n_head / attn_tc::kHeadsPerCta);
+      attn_tc::attention_tc_kernel<<<grid, attn_tc::kThreads, attn_tc::kSmemBytes, st>>>(tc_params);
+      prof_end(c, pi, attn_flops);
+      c->launches += 4;
+    } else {
       const int pi = prof_begin(c, PK_ATTN);
       dim3 grid(tiles, cf.n_head);
       if (W == 2) attn::attention_kernel<true><<<grid, attn::kThreads, attn::smem_bytes<true>(), st>>>(b_q, b_k, b_v, b_att, D * W, D, d_tiles, d_P, d_L);
