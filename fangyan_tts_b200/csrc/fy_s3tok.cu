@@ -518,3 +518,16 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
 }
 
 }  // extern "C"
+
+#ifdef FY_STALLPROF
+// Debug build only: copy the attention role-stall counters to the host (16 x u64) and optionally clear them.
+extern "C" int fy_debug_attn_stalls(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  if (cudaMemcpyFromSymbol(out, fy::attn_tc::g_attn_stall, sizeof(unsigned long long) * 16) != cudaSuccess) return 1;
+  if (reset) {
+    unsigned long long z[16] = {0};
+    if (cudaMemcpyToSymbol(fy::attn_tc::g_attn_stall, z, sizeof(z)) != cudaSuccess) return 1;
+  }
+  return 0;
+}
+#endif
