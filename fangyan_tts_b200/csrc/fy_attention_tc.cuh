@@ -1,17 +1,23 @@
-// Variable-length self-attention on tcgen05 (S3 encoder, row A9), split-bf16 mode.  FY_ATTN_TC=1 selects it.
+// Variable-length self-attention on tcgen05 (S3 encoder, row A9), split-bf16 mode.  FY_ATTN_TC=0 selects the
+// mma.sync kernel of fy_attention.cuh instead.
 //
-// One CTA = 128 query rows of one (utterance, head).  Both GEMMs of the flash loop run on the 5th-gen tensor cores
-// with fp32 accumulators in TMEM; the CUDA cores only do the softmax:
-//   warp 5, one thread : TMA loads (Q of each head into two alternating buffers; K/V 64-key tiles into a 3-stage ring)
-//   warp 4, one thread : every tcgen05.mma
+// One CTA = 128 query rows of one utterance, walked over kHeadsPerCta heads.  Both GEMMs of the flash loop run on the
+// 5th-gen tensor cores with fp32 accumulators in TMEM, and BOTH take their A operand from tensor memory (".ts" form):
+// Q is constant over a head's key tiles and P is produced by the softmax threads, so neither ever touches shared
+// memory -- the only operand bytes the shared-memory port serves are the K and V tiles (2 KB per MMA instead of 6 KB,
+// which is what held the all-shared-memory version at ~100 clk per M128 N64 K16 instruction against a 32 clk floor).
+//   warp 9, one thread : TMA loads of the K / V 64-key tiles (hi and lo halves) into a kStages ring
+//   warp 8, one thread : every tcgen05.mma
 //                        S_t = Q K_t^T   (M 128, N 64, K 64; three products hi*hi + hi*lo + lo*hi)
 //                        O_t = P_t V_t   (M 128, N 64, K 64 keys; V is consumed MN-major, i.e. exactly as the
 //                                         [key][d] tile TMA delivers it -- no transpose anywhere)
 //   warps 0-7, 2 threads per query row (32 keys each): tcgen05.ld of the S row, running max / sum in registers (the
 //                        two halves meet through shared memory once per tile, no shuffles), P = 2^(s log2e - m)
-//                        written to shared memory as bf16 hi | lo in the K-major 128-byte-swizzled layout the second
-//                        MMA reads, then O_t is read back from TMEM and folded into the register accumulator.
-// S is double-buffered in TMEM and P in shared memory, so S_{t+1} is computed while the softmax of tile t runs.
+//                        packed to bf16 hi | lo and stored to TMEM with tcgen05.st, then O_{t-1} is read back from
+//                        TMEM and folded into the register accumulator.  The same threads stage Q: each reads its
+//                        64 + 64 bytes of the next head's query row from global memory at the start of a head and
+//                        stores them to TMEM under the first tile's softmax.
+// S, P and Q are double-buffered in TMEM, so S_{t+1} is computed while the softmax of tile t runs.
 // Rows past the utterance inside a tile belong to the next utterance or a guard row: keys are masked, queries are
 // computed and not stored, V rows meet P = 0; all of it is finite data of the same buffers (the kernel keeps the
 // guard rows of its own output at zero for that reason).
@@ -22,20 +28,20 @@
 namespace fy {
 namespace attn_tc {
 
-constexpr int kBQ = 128, kBK = 64, kDH = 64, kThreads = 320, kStages = 3;
+constexpr int kBQ = 128, kBK = 64, kDH = 64, kThreads = 320, kStages = 4;
 constexpr int kSoftmaxThreads = 256;       // two threads per query row: keys / head-dim columns [0, 32) and [32, 64)
-constexpr int kQBytes = kBQ * 128;         // one [128][64] bf16 tile
 constexpr int kKVBytes = kBK * 128;        // one [64][64] bf16 tile
 constexpr int kStageBytes = 4 * kKVBytes;  // K hi, K lo, V hi, V lo
-constexpr int kPBytes = kBQ * 128;         // one [128][64] bf16 probability tile
 constexpr int kHeadsPerCta = 4;           // heads walked by one CTA (launch, TMEM allocation, pipeline fill paid once)
-constexpr int kTileBytes = 4 * kQBytes + kStages * kStageBytes + 4 * kPBytes;
+constexpr int kTileBytes = kStages * kStageBytes;
 constexpr int kCtrlBytes = 256 + 2 * 2 * kBQ * 4;      // barriers + TMEM holder, then the row max / sum exchange
-constexpr int kSmemBytes = 227 * 1024;                  // everything the SM has; what is left over is alignment slack
-constexpr int kAlignSlack = kSmemBytes - kTileBytes - kCtrlBytes;
-static_assert(kStages == 3, "barrier layout");
-static_assert(kAlignSlack >= 512, "shared memory budget");
-constexpr uint32_t kTmemCols = 256;        // S0 [0,64) S1 [64,128) O [128,192)
+constexpr int kSmemBytes = kTileBytes + kCtrlBytes + 1024;   // > half an SM's shared memory: one CTA per SM (TMEM is whole)
+constexpr int kAlignSlack = 1024;
+static_assert(kSmemBytes > 114 * 1024 && kSmemBytes <= 227 * 1024, "shared memory budget");
+// Tensor-memory columns: S0 [0,64) S1 [64,128) O [128,192) | P0 [192,256) P1 [256,320) | Q0 [320,384) Q1 [384,448);
+// a P / Q buffer is 32 columns of bf16 pairs (64 values) for the hi halves followed by 32 for the lo halves.
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kColO = 128, kColP = 192, kColQ = 320;
 
 // kind::f16 instruction descriptor, bf16 A (K-major) x bf16 B, fp32 D; b_mn = 1: B is MN-major.
 __host__ __device__ constexpr uint32_t idesc(uint32_t m, uint32_t n, uint32_t b_mn) {
@@ -54,14 +60,13 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
 __device__ __forceinline__ uint32_t pack_lo(uint32_t hi, float a, float b) {
   return pack2(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xffff0000u));
 }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 
 struct Params {
-  CUtensorMap tm_q;    // [rows, 2 D] bf16, box 64 cols x 128 rows
-  CUtensorMap tm_kv;   // same tensor geometry (k and v share ld), box 64 cols x 64 rows; bases differ -> two maps
+  CUtensorMap tm_kv;   // [rows, 2 D] bf16, box 64 cols x 64 rows; k and v share the geometry, bases differ -> two maps
   CUtensorMap tm_v;
+  const __nv_bfloat16* q;
   __nv_bfloat16* out;
-  int ld, lo_off;
+  int ld, lo_off, rows;
   const int2* tiles;   // (utterance, q0) per blockIdx.x, q0 a multiple of 128
   const int* utt_P;
   const int* utt_L;
@@ -80,24 +85,20 @@ __device__ unsigned long long g_attn_stall[16];
 __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t align_pad = (1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u;
-  if (align_pad > static_cast<uint32_t>(kAlignSlack)) __trap();   // dynamic shared memory starts 1024-aligned in practice
-  uint8_t* smem = smem_raw + align_pad;
-  uint8_t* sQ = smem;                              // buffer g & 1 of head g: hi | lo
-  uint8_t* sKV = sQ + 4 * kQBytes;                 // stage s: K hi, K lo, V hi, V lo
-  uint8_t* sP = sKV + kStages * kStageBytes;       // buffer b: P hi, P lo
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 4 * kPBytes);
-  uint64_t* q_full = bars;            // [2]
-  uint64_t* q_empty = bars + 2;       // [2]
-  uint64_t* k_full = bars + 4;        // [kStages]   K and V of a stage are tracked apart: K frees up as soon as S_t
-  uint64_t* k_empty = bars + 7;       // [kStages]   has been computed, a whole tile before P_t V_t, so its slot is
-  uint64_t* v_full = bars + 10;       // [kStages]   refilled that much earlier
-  uint64_t* v_empty = bars + 13;      // [kStages]
-  uint64_t* s_full = bars + 16;       // [2]
-  uint64_t* s_empty = bars + 18;      // [2]
-  uint64_t* p_full = bars + 20;       // [2]
-  uint64_t* o_full = bars + 22;       // 1
-  uint64_t* o_empty = bars + 23;      // 1
-  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 24);
+  uint8_t* sKV = smem_raw + align_pad;               // stage s: K hi, K lo, V hi, V lo
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + kStages * kStageBytes);
+  uint64_t* k_full = bars;                    // [kStages]   K and V of a stage are tracked apart: K frees up as soon
+  uint64_t* k_empty = bars + kStages;         // [kStages]   as S_t has been computed, a whole tile before P_t V_t, so
+  uint64_t* v_full = bars + 2 * kStages;      // [kStages]   its slot is refilled that much earlier
+  uint64_t* v_empty = bars + 3 * kStages;     // [kStages]
+  uint64_t* s_full = bars + 4 * kStages;      // [2]
+  uint64_t* s_empty = s_full + 2;             // [2]
+  uint64_t* p_full = s_full + 4;              // [2]
+  uint64_t* q_full = s_full + 6;              // [2]
+  uint64_t* o_full = s_full + 8;              // 1
+  uint64_t* o_empty = s_full + 9;             // 1
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(s_full + 10);
+  static_assert((4 * kStages + 11) * 8 <= 256, "barrier block");
   float* xch = reinterpret_cast<float*>(bars + 32);   // [2 (tile parity)][2 (half)][128 rows]: row max / row sum exchange
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -109,7 +110,6 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
   const int total = nkt * kHeadsPerCta;            // global tile index T = g * nkt + t: every ring / parity is keyed on T
 
   if (threadIdx.x == kSoftmaxThreads) {
-    ptx::prefetch_tmap(&p.tm_q);
     ptx::prefetch_tmap(&p.tm_kv);
     ptx::prefetch_tmap(&p.tm_v);
     for (int i = 0; i < kStages; ++i) {
@@ -119,11 +119,10 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       ptx::mbar_init(&v_empty[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(&q_full[i], 1);
-      ptx::mbar_init(&q_empty[i], 1);
       ptx::mbar_init(&s_full[i], 1);
       ptx::mbar_init(&s_empty[i], 8);
       ptx::mbar_init(&p_full[i], 8);
+      ptx::mbar_init(&q_full[i], 8);
     }
     ptx::mbar_init(o_full, 1);
     ptx::mbar_init(o_empty, 8);
@@ -137,18 +136,11 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
 
   if (warp == 9) {
     if (lane == 0) {
-      // ------------------------------------------------ TMA producer: Q per head (2 buffers), K/V tiles (ring)
+      // ------------------------------------------------ TMA producer: K / V tiles (ring)
       FY_AP(long long aw[16] = {0}; const long long aw_t0 = clock64();)
       for (int T = 0; T < total; ++T) {
         const int g = T / nkt, t = T - g * nkt;
         const int col = (h0 + g) * kDH;
-        if (t == 0) {
-          if (g >= 2) FY_AW(2, ptx::mbar_wait(&q_empty[g & 1], ((g >> 1) - 1) & 1))   // every S of head g - 2 has completed
-          uint8_t* d = sQ + (g & 1) * 2 * kQBytes;
-          ptx::mbar_expect_tx(&q_full[g & 1], 2 * kQBytes);
-          ptx::tma_load_2d(d, &p.tm_q, &q_full[g & 1], col, P + q0);
-          ptx::tma_load_2d(d + kQBytes, &p.tm_q, &q_full[g & 1], col + p.lo_off, P + q0);
-        }
         const int st = T % kStages;
         const uint32_t ph = ((T / kStages) - 1) & 1;
         uint8_t* d = sKV + st * kStageBytes;
@@ -172,37 +164,39 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       constexpr uint32_t id_o = idesc(kBQ, kDH, 1);   // O = P V  : V is MN-major ([key][d] rows of 128 bytes)
       auto issue_s = [&](int T) {
         const int g = T / nkt;
-        if (T == g * nkt) FY_AW(9, ptx::mbar_wait(&q_full[g & 1], (g >> 1) & 1))   // first tile of a head: its Q has landed
-        const uint32_t q_hi = ptx::smem_u32(sQ + (g & 1) * 2 * kQBytes), q_lo = q_hi + kQBytes;
+        if (T == g * nkt) {                            // first tile of a head: its Q has been stored to TMEM
+          FY_AW(9, ptx::mbar_wait(&q_full[g & 1], (g >> 1) & 1))
+          ptx::tc_fence_after();
+        }
+        const uint32_t qa = tmem + kColQ + (g & 1) * 64;
         const uint32_t kb = ptx::smem_u32(sKV + (T % kStages) * kStageBytes);
         const uint32_t d = tmem + (T & 1) * kBK;
         uint32_t acc = 0;
 #pragma unroll
         for (int pr = 0; pr < 3; ++pr) {
-          const uint64_t da = ptx::make_desc_sw128(pr == 2 ? q_lo : q_hi);
+          const uint32_t ta = qa + (pr == 2 ? 32 : 0);
           const uint64_t db = ptx::make_desc_sw128(kb + (pr == 1 ? kKVBytes : 0));
 #pragma unroll
-          for (int k = 0; k < kDH / 16; ++k) {
-            ptx::mma_bf16_ss(d, da + 2 * k, db + 2 * k, id_s, acc);
+          for (int k = 0; k < kDH / 16; ++k) {   // 16 head-dim values per step: 8 TMEM columns of Q, +32 bytes in K rows
+            ptx::mma_bf16_ts(d, ta + 8 * k, db + 2 * k, id_s, acc);
             acc = 1;
           }
         }
         ptx::mma_commit(&s_full[T & 1]);
         ptx::mma_commit(&k_empty[T % kStages]);
-        if (T == g * nkt + nkt - 1) ptx::mma_commit(&q_empty[g & 1]);   // last S of the head: its Q buffer frees up
       };
       auto issue_pv = [&](int T) {
         const uint32_t vb = ptx::smem_u32(sKV + (T % kStages) * kStageBytes) + 2 * kKVBytes;
-        const uint32_t pb = ptx::smem_u32(sP + (T & 1) * 2 * kPBytes);
-        const uint32_t d = tmem + 2 * kBK;
+        const uint32_t pa = tmem + kColP + (T & 1) * 64;
+        const uint32_t d = tmem + kColO;
         uint32_t acc = 0;
 #pragma unroll
         for (int pr = 0; pr < 3; ++pr) {
-          const uint64_t da = ptx::make_desc_sw128(pb + (pr == 2 ? kPBytes : 0));
+          const uint32_t ta = pa + (pr == 2 ? 32 : 0);
           const uint64_t db = ptx::make_desc_sw128(vb + (pr == 1 ? kKVBytes : 0));
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {   // 16 keys per step: +32 bytes in P rows, +16 rows (2048 B) in V
-            ptx::mma_bf16_ss(d, da + 2 * k, db + 128 * k, id_o, acc);
+          for (int k = 0; k < kBK / 16; ++k) {   // 16 keys per step: 8 TMEM columns of P, +16 rows (2048 B) in V
+            ptx::mma_bf16_ts(d, ta + 8 * k, db + 128 * k, id_o, acc);
             acc = 1;
           }
         }
@@ -238,11 +232,37 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
     constexpr int HC = kBK / 2;     // 32 keys (and 32 head-dim columns) per thread
     FY_AP(long long aw[16] = {0}; const long long aw_t0 = clock64();)
     float o[HC];
+    // Q staging: this thread owns head-dim values [32 half, 32 half + 32) of its query row, hi and lo halves
+    const bool q_row_ok = P + q0 + row < p.rows;
+    const __nv_bfloat16* q_src = p.q + (size_t)(q_row_ok ? P + q0 + row : 0) * p.ld + h0 * kDH + half * HC;
+    uint32_t qh[16], ql[16];
+    auto load_q = [&](int g) {
+      const uint4* a = reinterpret_cast<const uint4*>(q_src + g * kDH);
+      const uint4* b = reinterpret_cast<const uint4*>(q_src + g * kDH + p.lo_off);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const uint4 x = q_row_ok ? __ldg(a + c) : make_uint4(0u, 0u, 0u, 0u);
+        const uint4 y = q_row_ok ? __ldg(b + c) : make_uint4(0u, 0u, 0u, 0u);
+        qh[4 * c] = x.x; qh[4 * c + 1] = x.y; qh[4 * c + 2] = x.z; qh[4 * c + 3] = x.w;
+        ql[4 * c] = y.x; ql[4 * c + 1] = y.y; ql[4 * c + 2] = y.z; ql[4 * c + 3] = y.w;
+      }
+    };
+    auto store_q = [&](int g) {   // followed by tmem_st_wait + arrive by the caller
+      const uint32_t qa = t_row + kColQ + (g & 1) * 64 + half * 16;
+      ptx::tmem_st_32x16(qa, qh);
+      ptx::tmem_st_32x16(qa + 32, ql);
+    };
+    load_q(0);
+    store_q(0);
+    ptx::tmem_st_wait();
+    ptx::tc_fence_before();
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(&q_full[0]);
     auto fold_o = [&](int T) {   // o += O_T (o is already expressed relative to the maximum O_T was computed with)
       FY_AW(12, ptx::mbar_wait(o_full, T & 1))
       ptx::tc_fence_after();
       uint32_t ov[32];
-      ptx::tmem_ld_32x32(t_row + 2 * kBK + half * HC, ov);
+      ptx::tmem_ld_32x32(t_row + kColO + half * HC, ov);
       ptx::tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < HC; ++j) o[j] += __uint_as_float(ov[j]);
@@ -253,6 +273,9 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
 #pragma unroll 1
     for (int g = 0; g < kHeadsPerCta; ++g) {
       const int col = (h0 + g) * kDH + half * HC;
+      // The Q buffer of head g + 1 held head g - 1, whose S products all completed before the O of its last tile did
+      // (folded at the end of the previous iteration); the loads land while the first tile's softmax runs.
+      if (g + 1 < kHeadsPerCta) load_q(g + 1);
 #pragma unroll
       for (int j = 0; j < HC; ++j) o[j] = 0.f;
       float m = -INFINITY, l = 0.f;
@@ -293,23 +316,28 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
           sum += s[j];
         }
         l = l * corr + sum;                            // partial (this half's keys); the halves are added at the end
-        // P row -> shared memory, K-major SW128: chunk c (8 keys) of row r at r * 128 + ((c ^ (r & 7)) << 4)
-        uint8_t* ph = sP + (T & 1) * 2 * kPBytes + row * 128;
+        // P row -> tensor memory: keys [32 half, 32 half + 32) are columns [16 half, 16 half + 16) of the hi and of the
+        // lo block of buffer T & 1 (two bf16 per column, even key in the low half-word)
+        {
+          uint32_t ph[16], pl[16];
 #pragma unroll
-        for (int cc = 0; cc < 4; ++cc) {
-          const int c = half * 4 + cc;
-          uint4 hi, lo;
-          hi.x = pack2(s[8 * cc], s[8 * cc + 1]); hi.y = pack2(s[8 * cc + 2], s[8 * cc + 3]);
-          hi.z = pack2(s[8 * cc + 4], s[8 * cc + 5]); hi.w = pack2(s[8 * cc + 6], s[8 * cc + 7]);
-          lo.x = pack_lo(hi.x, s[8 * cc], s[8 * cc + 1]); lo.y = pack_lo(hi.y, s[8 * cc + 2], s[8 * cc + 3]);
-          lo.z = pack_lo(hi.z, s[8 * cc + 4], s[8 * cc + 5]); lo.w = pack_lo(hi.w, s[8 * cc + 6], s[8 * cc + 7]);
-          const int off = (c ^ (row & 7)) << 4;
-          *reinterpret_cast<uint4*>(ph + off) = hi;
-          *reinterpret_cast<uint4*>(ph + kPBytes + off) = lo;
+          for (int j = 0; j < 16; ++j) {
+            ph[j] = pack2(s[2 * j], s[2 * j + 1]);
+            pl[j] = pack_lo(ph[j], s[2 * j], s[2 * j + 1]);
+          }
+          const uint32_t pa = t_row + kColP + (T & 1) * 64 + half * 16;
+          ptx::tmem_st_32x16(pa, ph);
+          ptx::tmem_st_32x16(pa + 32, pl);
         }
-        fence_async_smem();
+        const bool stage_q = t == 0 && g + 1 < kHeadsPerCta;
+        if (stage_q) store_q(g + 1);
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&p_full[T & 1]);
+        if (lane == 0) {
+          ptx::mbar_arrive(&p_full[T & 1]);
+          if (stage_q) ptx::mbar_arrive(&q_full[(g + 1) & 1]);
+        }
         // Fold O_{t-1} (long finished: its MMA ran under this tile's softmax) into the running accumulator, one tile
         // late so that the tensor-core latency of P V is never waited for; then rescale for this tile's maximum.
         if (t > 0) fold_o(T - 1);
