@@ -258,6 +258,7 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
     ptx::tc_fence_before();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive(&q_full[0]);
+    if (kHeadsPerCta > 1) load_q(1);   // in flight until the first tile's P has been written
     auto fold_o = [&](int T) {   // o += O_T (o is already expressed relative to the maximum O_T was computed with)
       FY_AW(12, ptx::mbar_wait(o_full, T & 1))
       ptx::tc_fence_after();
@@ -270,85 +271,13 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(o_empty);
     };
-#pragma unroll 1
-    for (int g = 0; g < kHeadsPerCta; ++g) {
+    // Head epilogue: add the two halves' row sums (exchanged through shared memory between warps w and w + 4 only:
+    // named barrier 1 + wq, 64 threads), normalise, split to bf16 hi | lo and store.
+    auto finish_head = [&](int g, float l) {
       const int col = (h0 + g) * kDH + half * HC;
-      // The Q buffer of head g + 1 held head g - 1, whose S products all completed before the O of its last tile did
-      // (folded at the end of the previous iteration); the loads land while the first tile's softmax runs.
-      if (g + 1 < kHeadsPerCta) load_q(g + 1);
-#pragma unroll
-      for (int j = 0; j < HC; ++j) o[j] = 0.f;
-      float m = -INFINITY, l = 0.f;
-#pragma unroll 1
-      for (int t = 0; t < nkt; ++t) {
-        const int T = g * nkt + t;
-        FY_AW(11, ptx::mbar_wait(&s_full[T & 1], (T >> 1) & 1))
-        ptx::tc_fence_after();
-        uint32_t sv[32];
-        ptx::tmem_ld_32x32(t_row + (T & 1) * kBK + half * HC, sv);
-        ptx::tmem_ld_wait();
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&s_empty[T & 1]);
-        float s[HC];
-#pragma unroll
-        for (int j = 0; j < HC; ++j) s[j] = __uint_as_float(sv[j]);
-        if ((t + 1) * kBK > L) {
-#pragma unroll
-          for (int j = 0; j < HC; ++j)
-            if (t * kBK + half * HC + j >= L) s[j] = -INFINITY;
-        }
-        float mx = s[0];
-#pragma unroll
-        for (int j = 1; j < HC; ++j) mx = fmaxf(mx, s[j]);
-        // row maximum over both halves: exchanged through shared memory (slot T & 1, one named barrier per tile)
-        float* xm = xch + (T & 1) * 2 * kBQ;
-        xm[half * kBQ + row] = mx;
-        FY_AW(13, asm volatile("bar.sync 1, %0;\n" ::"n"(kSoftmaxThreads) : "memory"))
-        mx = fmaxf(mx, xm[(half ^ 1) * kBQ + row]);
-        const float m_new = fmaxf(m, mx * kLog2e);     // finite: every tile holds at least one valid key
-        const float corr = ex2(m - m_new);
-        m = m_new;
-        float sum = 0.f;
-#pragma unroll
-        for (int j = 0; j < HC; ++j) {
-          s[j] = ex2(fmaf(s[j], kLog2e, -m_new));
-          sum += s[j];
-        }
-        l = l * corr + sum;                            // partial (this half's keys); the halves are added at the end
-        // P row -> tensor memory: keys [32 half, 32 half + 32) are columns [16 half, 16 half + 16) of the hi and of the
-        // lo block of buffer T & 1 (two bf16 per column, even key in the low half-word)
-        {
-          uint32_t ph[16], pl[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            ph[j] = pack2(s[2 * j], s[2 * j + 1]);
-            pl[j] = pack_lo(ph[j], s[2 * j], s[2 * j + 1]);
-          }
-          const uint32_t pa = t_row + kColP + (T & 1) * 64 + half * 16;
-          ptx::tmem_st_32x16(pa, ph);
-          ptx::tmem_st_32x16(pa + 32, pl);
-        }
-        const bool stage_q = t == 0 && g + 1 < kHeadsPerCta;
-        if (stage_q) store_q(g + 1);
-        ptx::tmem_st_wait();
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) {
-          ptx::mbar_arrive(&p_full[T & 1]);
-          if (stage_q) ptx::mbar_arrive(&q_full[(g + 1) & 1]);
-        }
-        // Fold O_{t-1} (long finished: its MMA ran under this tile's softmax) into the running accumulator, one tile
-        // late so that the tensor-core latency of P V is never waited for; then rescale for this tile's maximum.
-        if (t > 0) fold_o(T - 1);
-#pragma unroll
-        for (int j = 0; j < HC; ++j) o[j] *= corr;
-      }
-      fold_o(g * nkt + nkt - 1);
-      // row sum = both halves (slot g & 1 of the exchange buffer; the next use of that slot is two barriers away)
-      float* xl = xch + (g & 1) * 2 * kBQ;
+      float* xl = xch + (g & 1) * 2 * kBQ;   // slot g & 1: its next use is two pair barriers away
       xl[half * kBQ + row] = l;
-      asm volatile("bar.sync 1, %0;\n" ::"n"(kSoftmaxThreads) : "memory");
+      FY_AW(13, asm volatile("bar.sync %0, 64;\n" ::"r"(1 + wq) : "memory"))
       l += xl[(half ^ 1) * kBQ + row];
       if (q0 + row < L) {
         const float inv = 1.0f / l;
@@ -378,7 +307,94 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
           *reinterpret_cast<uint4*>(dst + p.lo_off + 8 * c) = make_uint4(0u, 0u, 0u, 0u);
         }
       }
+    };
+    // One flat loop over the CTA's tiles T = g * nkt + t.  O_{T-1} is folded one tile late (after P_T has been handed
+    // to the tensor core), ALSO across a head boundary: the previous head's last fold, normalisation and store run
+    // under the first S / P V products of the next head instead of leaving the tensor pipe idle.
+#pragma unroll
+    for (int j = 0; j < HC; ++j) o[j] = 0.f;
+    float m = -INFINITY, l = 0.f, l_prev = 0.f;
+    int g = 0, t = 0;
+#pragma unroll 1
+    for (int T = 0; T < total; ++T) {
+      if (t == 0) { l_prev = l; l = 0.f; m = -INFINITY; }
+      FY_AW(11, ptx::mbar_wait(&s_full[T & 1], (T >> 1) & 1))
+      ptx::tc_fence_after();
+      // the whole 64-key row is read: the other half only for the row maximum (no exchange, no barrier in the loop)
+      uint32_t sv[32], sw[32];
+      ptx::tmem_ld_32x32(t_row + (T & 1) * kBK + (half ^ 1) * HC, sw);
+      ptx::tmem_ld_32x32(t_row + (T & 1) * kBK + half * HC, sv);
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&s_empty[T & 1]);
+      float s[HC];
+#pragma unroll
+      for (int j = 0; j < HC; ++j) s[j] = __uint_as_float(sv[j]);
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      if ((t + 1) * kBK > L) {
+#pragma unroll
+        for (int j = 0; j < HC; ++j) {
+          if (t * kBK + half * HC + j >= L) s[j] = -INFINITY;
+          if (t * kBK + (half ^ 1) * HC + j < L) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(sw[j]));
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < HC; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(sw[j]));
+      }
+#pragma unroll
+      for (int j = 0; j < HC; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], s[j]);
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      const float m_new = fmaxf(m, mx * kLog2e);     // finite: every tile holds at least one valid key
+      const float corr = ex2(m - m_new);             // 0 on the first tile of a head (m = -inf)
+      m = m_new;
+      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int j = 0; j < HC; ++j) {
+        s[j] = ex2(fmaf(s[j], kLog2e, -m_new));
+        sum4[j & 3] += s[j];
+      }
+      l = l * corr + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));   // partial (this half's keys)
+      // P row -> tensor memory: keys [32 half, 32 half + 32) are columns [16 half, 16 half + 16) of the hi and of the
+      // lo block of buffer T & 1 (two bf16 per column, even key in the low half-word)
+      {
+        uint32_t ph[16], pl[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          ph[j] = pack2(s[2 * j], s[2 * j + 1]);
+          pl[j] = pack_lo(ph[j], s[2 * j], s[2 * j + 1]);
+        }
+        const uint32_t pa = t_row + kColP + (T & 1) * 64 + half * 16;
+        ptx::tmem_st_32x16(pa, ph);
+        ptx::tmem_st_32x16(pa + 32, pl);
+      }
+      // Q of the next head goes into the buffer head g - 1 used: s_full of this tile implies every earlier product
+      // (all S of head g - 1) has completed.
+      const bool stage_q = t == 0 && g + 1 < kHeadsPerCta;
+      if (stage_q) store_q(g + 1);
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        ptx::mbar_arrive(&p_full[T & 1]);
+        if (stage_q) ptx::mbar_arrive(&q_full[(g + 1) & 1]);
+      }
+      if (stage_q && g + 2 < kHeadsPerCta) load_q(g + 2);
+      // Fold O_{T-1} (long finished: its MMA ran under this tile's softmax) into the running accumulator, one tile
+      // late so that the tensor-core latency of P V is never waited for; then rescale for this tile's maximum.
+      if (T > 0) fold_o(T - 1);
+      if (t == 0) {
+        if (T > 0) finish_head(g - 1, l_prev);
+#pragma unroll
+        for (int j = 0; j < HC; ++j) o[j] = 0.f;
+      } else {
+#pragma unroll
+        for (int j = 0; j < HC; ++j) o[j] *= corr;
+      }
+      if (++t == nkt) { t = 0; ++g; }
     }
+    fold_o(total - 1);
+    finish_head(kHeadsPerCta - 1, l);
     FY_AP(if (threadIdx.x == 0) {
       for (int i = 11; i < 14; ++i) atomicAdd(&g_attn_stall[i], (unsigned long long)aw[i]);
       atomicAdd(&g_attn_stall[14], (unsigned long long)(clock64() - aw_t0));
