@@ -157,8 +157,9 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
             atomicAdd(&g_attn_stall[3], (unsigned long long)(clock64() - aw_t0));)
     }
   } else if (warp == 8) {
-    if (lane == 0) {
-      // ------------------------------------------------ every MMA
+    {
+      // ------------------------------------------------ every MMA.  The whole warp runs this loop (waits included) and
+      // one elected lane issues each instruction: see ptx::mma_bf16_ts_elect.
       FY_AP(long long aw[16] = {0}; const long long aw_t0 = clock64();)
       constexpr uint32_t id_s = idesc(kBQ, kBK, 0);   // S = Q K^T: both operands K-major
       constexpr uint32_t id_o = idesc(kBQ, kDH, 1);   // O = P V  : V is MN-major ([key][d] rows of 128 bytes)
@@ -178,12 +179,12 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
           const uint64_t db = ptx::make_desc_sw128(kb + (pr == 1 ? kKVBytes : 0));
 #pragma unroll
           for (int k = 0; k < kDH / 16; ++k) {   // 16 head-dim values per step: 8 TMEM columns of Q, +32 bytes in K rows
-            ptx::mma_bf16_ts(d, ta + 8 * k, db + 2 * k, id_s, acc);
+            ptx::mma_bf16_ts_elect(d, ta + 8 * k, db + 2 * k, id_s, acc);
             acc = 1;
           }
         }
-        ptx::mma_commit(&s_full[T & 1]);
-        ptx::mma_commit(&k_empty[T % kStages]);
+        ptx::mma_commit_elect(&s_full[T & 1]);
+        ptx::mma_commit_elect(&k_empty[T % kStages]);
       };
       auto issue_pv = [&](int T) {
         const uint32_t vb = ptx::smem_u32(sKV + (T % kStages) * kStageBytes) + 2 * kKVBytes;
@@ -196,12 +197,12 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
           const uint64_t db = ptx::make_desc_sw128(vb + (pr == 1 ? kKVBytes : 0));
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k) {   // 16 keys per step: 8 TMEM columns of P, +16 rows (2048 B) in V
-            ptx::mma_bf16_ts(d, ta + 8 * k, db + 128 * k, id_o, acc);
+            ptx::mma_bf16_ts_elect(d, ta + 8 * k, db + 128 * k, id_o, acc);
             acc = 1;
           }
         }
-        ptx::mma_commit(o_full);
-        ptx::mma_commit(&v_empty[T % kStages]);
+        ptx::mma_commit_elect(o_full);
+        ptx::mma_commit_elect(&v_empty[T % kStages]);
       };
       FY_AW(4, ptx::mbar_wait(&k_full[0], 0))
       ptx::tc_fence_after();
@@ -219,9 +220,11 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
         ptx::tc_fence_after();
         issue_pv(T);
       }
-      FY_AP(for (int i = 4; i < 10; ++i) atomicAdd(&g_attn_stall[i], (unsigned long long)aw[i]);
-            atomicAdd(&g_attn_stall[10], (unsigned long long)(clock64() - aw_t0));
-            atomicAdd(&g_attn_stall[15], 1ull);)
+      FY_AP(if (lane == 0) {
+        for (int i = 4; i < 10; ++i) atomicAdd(&g_attn_stall[i], (unsigned long long)aw[i]);
+        atomicAdd(&g_attn_stall[10], (unsigned long long)(clock64() - aw_t0));
+        atomicAdd(&g_attn_stall[15], 1ull);
+      })
     }
   } else {
     // ------------------------------------------------ softmax: two threads per query row (warps w and w + 4)

@@ -225,7 +225,9 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0 && cta_rank == 0) {
+    // The whole warp runs the loop (waits included); one elected lane issues each instruction (ptx::*_elect): a
+    // tcgen05.mma under "if (lane == 0)" costs ~50 clk to issue, which the N = 32 / 64 tiles cannot hide.
+    if (cta_rank == 0) {
       constexpr uint32_t idesc = TF32 ? ptx::make_idesc_tf32(TM, BN)
                                       : (OP == OP_F16 ? ptx::make_idesc_f16(TM, BN) : ptx::make_idesc_bf16(TM, BN));
       int stage = 0;
@@ -260,13 +262,13 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
                 const uint64_t da = pr == 2 ? a_lo : a_hi, db = pr == 1 ? b_lo : b_hi;
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k) {
-                  if (PAIR) ptx::mma_bf16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
-                  else ptx::mma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+                  if (PAIR) ptx::mma_bf16_ss_pair_elect(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+                  else ptx::mma_bf16_ss_elect(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
                   accumulate = 1;
                 }
               }
-              if (PAIR) { ptx::mma_commit_pair(&empty_bar[stage]); ptx::mma_commit_pair(&empty_bar[stage + 1]); }
-              else { ptx::mma_commit(&empty_bar[stage]); ptx::mma_commit(&empty_bar[stage + 1]); }
+              if (PAIR) { ptx::mma_commit_pair_elect(&empty_bar[stage]); ptx::mma_commit_pair_elect(&empty_bar[stage + 1]); }
+              else { ptx::mma_commit_elect(&empty_bar[stage]); ptx::mma_commit_elect(&empty_bar[stage + 1]); }
               stage += 2;
               if (stage == C::kStages) { stage = 0; phase ^= 1; }
             }
@@ -282,23 +284,23 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
             const uint64_t db = ptx::make_desc_sw128(a_addr + C::kABytes);
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
-              if (PAIR) ptx::mma_bf16_ss_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
-              else if (TF32) ptx::mma_tf32_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
-              else ptx::mma_bf16_ss(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              if (PAIR) ptx::mma_bf16_ss_pair_elect(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              else if (TF32) ptx::mma_tf32_ss_elect(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
+              else ptx::mma_bf16_ss_elect(d_tmem, da + 2 * k, db + 2 * k, idesc, accumulate);
               accumulate = 1;
             }
-            if (PAIR) ptx::mma_commit_pair(&empty_bar[stage]);
-            else ptx::mma_commit(&empty_bar[stage]);
+            if (PAIR) ptx::mma_commit_pair_elect(&empty_bar[stage]);
+            else ptx::mma_commit_elect(&empty_bar[stage]);
             if (++stage == C::kStages) { stage = 0; phase ^= 1; }
           }
         }
-        if (PAIR) ptx::mma_commit_pair(&tfull_bar[as]);
-        else ptx::mma_commit(&tfull_bar[as]);
+        if (PAIR) ptx::mma_commit_pair_elect(&tfull_bar[as]);
+        else ptx::mma_commit_elect(&tfull_bar[as]);
         if (++as == C::kAccStages) { as = 0; aphase ^= 1; }
       }
-      FY_SP(atomicAdd(&g_stall[sp_slot + 2], (unsigned long long)sp_wf);
-            atomicAdd(&g_stall[sp_slot + 3], (unsigned long long)sp_we);
-            atomicAdd(&g_stall[sp_slot + 4], (unsigned long long)(clock64() - sp_t0));)
+      FY_SP(if (lane == 0) { atomicAdd(&g_stall[sp_slot + 2], (unsigned long long)sp_wf);
+                             atomicAdd(&g_stall[sp_slot + 3], (unsigned long long)sp_we);
+                             atomicAdd(&g_stall[sp_slot + 4], (unsigned long long)(clock64() - sp_t0)); })
     }
   } else if (warp >= 4) {
     // ===================== epilogue (warp w drains TMEM lane quarter w % 4; warps 8..11 take the upper columns) ====

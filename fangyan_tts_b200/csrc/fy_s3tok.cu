@@ -431,8 +431,9 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   FY_TRY(make_tmap_bf16(&m_att, b_att, Rtok, D * W, D * W, 128));
   FY_TRY(make_tmap_bf16(&m_h, b_h, Rtok, F * W, F * W, 128));
   FY_CHECK(D == 1280, FY_ERR_ARG, "layernorm kernel is instantiated for d_model == 1280 only (got %d)", D);
-  // tcgen05 attention (FY_ATTN_TC=1, split-bf16 only): TMA views of q, k, v and the 128-row tile list
-  static const bool attn_tc_env = [] { const char* e = getenv("FY_ATTN_TC"); return e && e[0] == '1'; }();
+  // tcgen05 attention (split-bf16 only; FY_ATTN_TC=0 falls back to the mma.sync kernel): TMA views of k, v and the
+  // 128-row tile list
+  static const bool attn_tc_env = [] { const char* e = getenv("FY_ATTN_TC"); return !(e && e[0] == '0'); }();
   const bool attn_tc_on = attn_tc_env && W == 2 && cf.d_model / cf.n_head == 64 && cf.n_head % attn_tc::kHeadsPerCta == 0;
   attn_tc::Params tc_params;
   if (attn_tc_on) {

@@ -66,3 +66,48 @@ def test_s3tok_matches_oracle(n_layer, prec, tol):
             assert d < 1e-3, (i, float(d))
         assert match >= 0.999 or ref_ids.numel() < 2000
     eng.close()
+
+
+_ALT_ATTENTION = r"""
+import json, sys
+import numpy as np, torch
+sys.path.insert(0, sys.argv[1])
+from fangyan_tts_b200 import synth, synth_weights
+from fangyan_tts_b200.configs import S3Config
+from fangyan_tts_b200.engine import Engine
+cfg = S3Config(n_layer=2)
+eng = Engine(0, "bf16x3")
+eng.load_s3tok(synth_weights.s3tok_state(cfg, seed=5), cfg)
+utts = synth.make_set(12, 23, 0.3, 9.0)
+lens = [len(u) for u in utts]
+pcm = torch.from_numpy(np.concatenate(utts)).cuda()
+mel, frames = eng.logmel(pcm, lens)
+tok, counts, pre = eng.s3tok(mel, frames, want_pre=True)
+torch.cuda.synchronize()
+print(json.dumps({"tok": tok.cpu().tolist(), "counts": list(counts), "pre": pre.cpu().flatten().tolist()}))
+"""
+
+
+def test_both_attention_kernels_agree():
+    """The tcgen05 kernel (default) and the mma.sync kernel (FY_ATTN_TC=0) compute the same attention: pre-FSQ
+    activations within 2e-4 of each other, token ids >= 99.9 % equal, counts bit-exact.  The switch is read once per
+    process, so each kernel runs in its own interpreter."""
+    import json
+    import os
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = str(Path(__file__).resolve().parent.parent)
+    out = {}
+    for v in ("1", "0"):
+        env = dict(os.environ, FY_ATTN_TC=v)
+        r = subprocess.run([sys.executable, "-c", _ALT_ATTENTION, root], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        out[v] = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["1"]["counts"] == out["0"]["counts"]
+    a, b = np.asarray(out["1"]["pre"]), np.asarray(out["0"]["pre"])
+    assert a.shape == b.shape and np.isfinite(a).all()
+    assert float(np.abs(a - b).max()) <= 2e-4
+    ta, tb = np.asarray(out["1"]["tok"]), np.asarray(out["0"]["tok"])
+    assert float((ta == tb).mean()) >= 0.999

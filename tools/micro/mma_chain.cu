@@ -53,6 +53,73 @@ __global__ void __launch_bounds__(128, 1) chain_kernel(long long* out, int slot)
   if (threadIdx.x < 32) { ptx::tc_fence_after(); ptx::tmem_dealloc<512>(tmem); }
 }
 
+// Same instruction stream issued two ways, optionally with 16 warps of dependent FP32 work sharing the schedulers:
+//   CONV = false: "if (threadIdx.x == issuer)" -- the compiler wraps every uniform-datapath UTCHMMA of a divergent
+//                 thread in an ELECT / BRA.U.ANY loop;
+//   CONV = true : the whole warp runs the loop, the instruction itself is predicated on elect.sync.
+__device__ __forceinline__ void mma_ts_elect(uint32_t d, uint32_t a, uint64_t db, uint32_t id, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}\n" ::"r"(d),
+      "r"(a), "l"(db), "r"(id), "r"(acc)
+      : "memory");
+}
+template <bool CONV, int BUSY>
+__global__ void __launch_bounds__(32 + 32 * 16, 1) issue_kernel(long long* out, int slot, float* sink) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t holder;
+  __shared__ volatile int done;
+  for (int i = threadIdx.x; i < 32768 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  if (threadIdx.x == 0) { ptx::mbar_init(&bar, 1); ptx::fence_mbar_init(); done = 0; }
+  if (threadIdx.x < 32) ptx::tmem_alloc<512>(&holder);
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = holder;
+  constexpr uint32_t id = idesc(128, 64);
+  constexpr int kIters = 384;
+  if (threadIdx.x < 32) {
+    const uint64_t db = ptx::make_desc_sw128(ptx::smem_u32(smem));
+    if (CONV) {
+      const long long t0 = clock64();
+#pragma unroll 12
+      for (int i = 0; i < kIters; ++i) mma_ts_elect(tmem + (i / 12 % 3) * 64, tmem + 448 + 8 * (i & 3), db + 2 * (i & 3), id, i % 12 != 0);
+      if (ptx::elect_one()) ptx::mma_commit(&bar);
+      ptx::mbar_wait(&bar, 0);
+      if (threadIdx.x == 0) out[slot] = (clock64() - t0) / kIters;
+    } else if (threadIdx.x == 0) {
+      const long long t0 = clock64();
+#pragma unroll 12
+      for (int i = 0; i < kIters; ++i) ptx::mma_bf16_ts(tmem + (i / 12 % 3) * 64, tmem + 448 + 8 * (i & 3), db + 2 * (i & 3), id, i % 12 != 0);
+      ptx::mma_commit(&bar);
+      ptx::mbar_wait(&bar, 0);
+      out[slot] = (clock64() - t0) / kIters;
+    }
+    __syncwarp();
+    if (threadIdx.x == 0) done = 1;
+  } else if (BUSY) {
+    float a = threadIdx.x, b = 1.0001f, c = 0.5f, d = 0.25f;
+    while (!done) {
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { a = fmaf(a, b, c); d = fmaf(d, b, a); c = fmaf(c, b, d); }
+    }
+    if (a + c + d == 12345.f) *sink = a;
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x < 32) { ptx::tc_fence_after(); ptx::tmem_dealloc<512>(tmem); }
+}
+template <bool CONV, int BUSY>
+void run_issue(long long* d_out, int slot, float* sink) {
+  cudaFuncSetAttribute(issue_kernel<CONV, BUSY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+  issue_kernel<CONV, BUSY><<<1, 32 + 32 * 16, 64 * 1024>>>(d_out, slot, sink);
+}
+
 template <int N, int NACC, bool TS>
 void run(long long* d_out, int slot) {
   cudaFuncSetAttribute(chain_kernel<N, NACC, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
@@ -69,6 +136,11 @@ int main() {
   run<128, 1, false>(d_out, s++); run<128, 2, false>(d_out, s++); run<128, 1, true>(d_out, s++); run<128, 2, true>(d_out, s++);
   run<256, 1, false>(d_out, s++); run<256, 1, true>(d_out, s++);
   run<32, 1, true>(d_out, s++); run<32, 4, true>(d_out, s++);
+  const int s_issue = s;
+  float* sink;
+  cudaMalloc(&sink, 4);
+  run_issue<false, 0>(d_out, s++, sink); run_issue<false, 1>(d_out, s++, sink);
+  run_issue<true, 0>(d_out, s++, sink); run_issue<true, 1>(d_out, s++, sink);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
   long long h[64];
@@ -76,6 +148,10 @@ int main() {
   const char* names[] = {"N64 acc1 SS", "N64 acc2 SS", "N64 acc4 SS", "N64 acc1 TS", "N64 acc2 TS", "N64 acc4 TS",
                          "N128 acc1 SS", "N128 acc2 SS", "N128 acc1 TS", "N128 acc2 TS", "N256 acc1 SS", "N256 acc1 TS",
                          "N32 acc1 TS", "N32 acc4 TS"};
+  const char* inames[] = {"lane-0 branch, idle SM", "lane-0 branch, 16 busy warps", "converged + elect, idle SM",
+                          "converged + elect, 16 busy warps"};
+  for (int i = s_issue; i < s; ++i) printf("N64 TS, 12-long chains, %-34s %lld clk / mma\n", inames[i - s_issue], h[i]);
+  s = s_issue;
   for (int i = 0; i < s; ++i) printf("%-14s %lld clk / mma (floor %d)\n", names[i], h[i], 128 * atoi(names[i] + 1) / 256);
   return 0;
 }
