@@ -11,13 +11,17 @@
 //                        S_t = Q K_t^T   (M 128, N 64, K 64; three products hi*hi + hi*lo + lo*hi)
 //                        O_t = P_t V_t   (M 128, N 64, K 64 keys; V is consumed MN-major, i.e. exactly as the
 //                                         [key][d] tile TMA delivers it -- no transpose anywhere)
-//   warps 0-7, 2 threads per query row (32 keys each): tcgen05.ld of the S row, running max / sum in registers (the
-//                        two halves meet through shared memory once per tile, no shuffles), P = 2^(s log2e - m)
-//                        packed to bf16 hi | lo and stored to TMEM with tcgen05.st, then O_{t-1} is read back from
-//                        TMEM and folded into the register accumulator.  The same threads stage Q: each reads its
-//                        64 + 64 bytes of the next head's query row from global memory at the start of a head and
-//                        stores them to TMEM under the first tile's softmax.
-// S, P and Q are double-buffered in TMEM, so S_{t+1} is computed while the softmax of tile t runs.
+//                        O accumulates in TMEM over a head's tiles (two buffers, alternating by head).
+//   warps 0-7, 2 threads per query row (32 keys each): every thread reads the whole 64-key S row from TMEM for the row
+//                        maximum (no exchange, no barrier in the loop), exponentiates its 32 keys, packs
+//                        P = 2^(s log2e - m) to bf16 hi | lo and stores it to TMEM with tcgen05.st.  The running
+//                        maximum m only moves when the new one exceeds it by more than 2^8 (P stays <= 256, which the
+//                        hi | lo split carries exactly); only then is O rescaled in TMEM (tcgen05.ld / st of the
+//                        thread's 32 columns) -- about once per head instead of a read-back every tile.  The same
+//                        threads stage Q: each reads its 64 + 64 bytes of the next head's query row from global memory
+//                        a head ahead and stores them to TMEM under a first tile's softmax.
+// S, P, Q and O are double-buffered in TMEM (all 512 columns): S_{t+1} is computed while the softmax of tile t runs,
+// and a head is normalised and stored under the first products of the next head.
 // Rows past the utterance inside a tile belong to the next utterance or a guard row: keys are masked, queries are
 // computed and not stored, V rows meet P = 0; all of it is finite data of the same buffers (the kernel keeps the
 // guard rows of its own output at zero for that reason).
@@ -38,10 +42,12 @@ constexpr int kCtrlBytes = 256 + 2 * 2 * kBQ * 4;      // barriers + TMEM holder
 constexpr int kSmemBytes = kTileBytes + kCtrlBytes + 1024;   // > half an SM's shared memory: one CTA per SM (TMEM is whole)
 constexpr int kAlignSlack = 1024;
 static_assert(kSmemBytes > 114 * 1024 && kSmemBytes <= 227 * 1024, "shared memory budget");
-// Tensor-memory columns: S0 [0,64) S1 [64,128) O [128,192) | P0 [192,256) P1 [256,320) | Q0 [320,384) Q1 [384,448);
-// a P / Q buffer is 32 columns of bf16 pairs (64 values) for the hi halves followed by 32 for the lo halves.
+// Tensor-memory columns: S0 [0,64) S1 [64,128) | O0 [128,192) O1 [192,256) | P0 [256,320) P1 [320,384) |
+// Q0 [384,448) Q1 [448,512); a P / Q buffer is 32 columns of bf16 pairs (64 values) for the hi halves followed by 32
+// for the lo halves.
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kColO = 128, kColP = 192, kColQ = 320;
+constexpr uint32_t kColO = 128, kColP = 256, kColQ = 384;
+constexpr float kRescaleSlack = 8.0f;      // log2 units the running maximum may lag behind before O is rescaled
 
 // kind::f16 instruction descriptor, bf16 A (K-major) x bf16 B, fp32 D; b_mn = 1: B is MN-major.
 __host__ __device__ constexpr uint32_t idesc(uint32_t m, uint32_t n, uint32_t b_mn) {
@@ -95,10 +101,11 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
   uint64_t* s_empty = s_full + 2;             // [2]
   uint64_t* p_full = s_full + 4;              // [2]
   uint64_t* q_full = s_full + 6;              // [2]
-  uint64_t* o_full = s_full + 8;              // 1
-  uint64_t* o_empty = s_full + 9;             // 1
-  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(s_full + 10);
-  static_assert((4 * kStages + 11) * 8 <= 256, "barrier block");
+  uint64_t* o_empty = s_full + 8;             // [2]  O buffer g & 1 has been read out (head g normalised)
+  uint64_t* o_full = s_full + 10;             // 1    one phase per P V product group
+  uint64_t* all_done = s_full + 11;           // 1    every product of the CTA has completed
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(s_full + 12);
+  static_assert((4 * kStages + 13) * 8 <= 256, "barrier block");
   float* xch = reinterpret_cast<float*>(bars + 32);   // [2 (tile parity)][2 (half)][128 rows]: row max / row sum exchange
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -124,8 +131,10 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       ptx::mbar_init(&p_full[i], 8);
       ptx::mbar_init(&q_full[i], 8);
     }
+    ptx::mbar_init(&o_empty[0], 8);
+    ptx::mbar_init(&o_empty[1], 8);
     ptx::mbar_init(o_full, 1);
-    ptx::mbar_init(o_empty, 8);
+    ptx::mbar_init(all_done, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 0) ptx::tmem_alloc<kTmemCols>(tmem_holder);
@@ -163,9 +172,8 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       FY_AP(long long aw[16] = {0}; const long long aw_t0 = clock64();)
       constexpr uint32_t id_s = idesc(kBQ, kBK, 0);   // S = Q K^T: both operands K-major
       constexpr uint32_t id_o = idesc(kBQ, kDH, 1);   // O = P V  : V is MN-major ([key][d] rows of 128 bytes)
-      auto issue_s = [&](int T) {
-        const int g = T / nkt;
-        if (T == g * nkt) {                            // first tile of a head: its Q has been stored to TMEM
+      auto issue_s = [&](int T, int g, int t) {
+        if (t == 0) {                                  // first tile of a head: its Q has been stored to TMEM
           FY_AW(9, ptx::mbar_wait(&q_full[g & 1], (g >> 1) & 1))
           ptx::tc_fence_after();
         }
@@ -186,11 +194,11 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
         ptx::mma_commit_elect(&s_full[T & 1]);
         ptx::mma_commit_elect(&k_empty[T % kStages]);
       };
-      auto issue_pv = [&](int T) {
+      auto issue_pv = [&](int T, int g, int t) {
         const uint32_t vb = ptx::smem_u32(sKV + (T % kStages) * kStageBytes) + 2 * kKVBytes;
         const uint32_t pa = tmem + kColP + (T & 1) * 64;
-        const uint32_t d = tmem + kColO;
-        uint32_t acc = 0;
+        const uint32_t d = tmem + kColO + (g & 1) * 64;
+        uint32_t acc = t > 0;                          // a head's first tile overwrites its O buffer
 #pragma unroll
         for (int pr = 0; pr < 3; ++pr) {
           const uint32_t ta = pa + (pr == 2 ? 32 : 0);
@@ -206,20 +214,25 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       };
       FY_AW(4, ptx::mbar_wait(&k_full[0], 0))
       ptx::tc_fence_after();
-      issue_s(0);
+      issue_s(0, 0, 0);
+      int g = 0, t = 0;        // of tile T
+      int g1 = 0, t1 = 0;      // of tile T + 1
       for (int T = 0; T < total; ++T) {
+        if (++t1 == nkt) { t1 = 0; ++g1; }
         if (T + 1 < total) {
           FY_AW(4, ptx::mbar_wait(&k_full[(T + 1) % kStages], ((T + 1) / kStages) & 1))
           if (T + 1 >= 2) FY_AW(5, ptx::mbar_wait(&s_empty[(T + 1) & 1], (((T + 1) >> 1) - 1) & 1))
           ptx::tc_fence_after();
-          issue_s(T + 1);
+          issue_s(T + 1, g1, t1);
         }
         FY_AW(6, ptx::mbar_wait(&v_full[T % kStages], (T / kStages) & 1))
         FY_AW(7, ptx::mbar_wait(&p_full[T & 1], (T >> 1) & 1))
-        if (T >= 1) FY_AW(8, ptx::mbar_wait(o_empty, (T - 1) & 1))
+        if (t == 0 && g >= 2) FY_AW(8, ptx::mbar_wait(&o_empty[g & 1], ((g >> 1) - 1) & 1))   // head g - 2 read out
         ptx::tc_fence_after();
-        issue_pv(T);
+        issue_pv(T, g, t);
+        g = g1; t = t1;
       }
+      ptx::mma_commit_elect(all_done);
       FY_AP(if (lane == 0) {
         for (int i = 4; i < 10; ++i) atomicAdd(&g_attn_stall[i], (unsigned long long)aw[i]);
         atomicAdd(&g_attn_stall[10], (unsigned long long)(clock64() - aw_t0));
@@ -234,7 +247,6 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
     const float kLog2e = 1.4426950408889634f;
     constexpr int HC = kBK / 2;     // 32 keys (and 32 head-dim columns) per thread
     FY_AP(long long aw[16] = {0}; const long long aw_t0 = clock64();)
-    float o[HC];
     // Q staging: this thread owns head-dim values [32 half, 32 half + 32) of its query row, hi and lo halves
     const bool q_row_ok = P + q0 + row < p.rows;
     const __nv_bfloat16* q_src = p.q + (size_t)(q_row_ok ? P + q0 + row : 0) * p.ld + h0 * kDH + half * HC;
@@ -261,23 +273,18 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
     ptx::tc_fence_before();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive(&q_full[0]);
-    if (kHeadsPerCta > 1) load_q(1);   // in flight until the first tile's P has been written
-    auto fold_o = [&](int T) {   // o += O_T (o is already expressed relative to the maximum O_T was computed with)
-      FY_AW(12, ptx::mbar_wait(o_full, T & 1))
-      ptx::tc_fence_after();
-      uint32_t ov[32];
-      ptx::tmem_ld_32x32(t_row + kColO + half * HC, ov);
-      ptx::tmem_ld_wait();
-#pragma unroll
-      for (int j = 0; j < HC; ++j) o[j] += __uint_as_float(ov[j]);
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(o_empty);
-    };
-    // Head epilogue: add the two halves' row sums (exchanged through shared memory between warps w and w + 4 only:
-    // named barrier 1 + wq, 64 threads), normalise, split to bf16 hi | lo and store.
+    // Head epilogue (the caller has waited for the head's last P V): read this thread's 32 O columns, add the two
+    // halves' row sums (exchanged through shared memory between warps w and w + 4 only: named barrier 1 + wq,
+    // 64 threads), normalise, split to bf16 hi | lo and store.
     auto finish_head = [&](int g, float l) {
       const int col = (h0 + g) * kDH + half * HC;
+      ptx::tc_fence_after();
+      uint32_t ov[32];
+      ptx::tmem_ld_32x32(t_row + kColO + (g & 1) * 64 + half * HC, ov);
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&o_empty[g & 1]);
       float* xl = xch + (g & 1) * 2 * kBQ;   // slot g & 1: its next use is two pair barriers away
       xl[half * kBQ + row] = l;
       FY_AW(13, asm volatile("bar.sync %0, 64;\n" ::"r"(1 + wq) : "memory"))
@@ -289,7 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
         for (int c = 0; c < 4; ++c) {
           float a[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) a[j] = o[8 * c + j] * inv;
+          for (int j = 0; j < 8; ++j) a[j] = __uint_as_float(ov[8 * c + j]) * inv;
           uint4 hi, lo;
           hi.x = pack2(a[0], a[1]); hi.y = pack2(a[2], a[3]); hi.z = pack2(a[4], a[5]); hi.w = pack2(a[6], a[7]);
           lo.x = pack_lo(hi.x, a[0], a[1]); lo.y = pack_lo(hi.y, a[2], a[3]);
@@ -311,16 +318,19 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
         }
       }
     };
-    // One flat loop over the CTA's tiles T = g * nkt + t.  O_{T-1} is folded one tile late (after P_T has been handed
-    // to the tensor core), ALSO across a head boundary: the previous head's last fold, normalisation and store run
-    // under the first S / P V products of the next head instead of leaving the tensor pipe idle.
-#pragma unroll
-    for (int j = 0; j < HC; ++j) o[j] = 0.f;
+    // One flat loop over the CTA's tiles T = g * nkt + t.  A head's normalisation and store are deferred to the first
+    // tile of the next head (after its P has been handed to the tensor core), so they run under S / P V products
+    // instead of leaving the tensor pipe idle.  Inside the loop o_full is only waited for BEFORE this warp's p_full
+    // arrival of the current tile T >= 1: P_T V_T cannot have been issued yet and s_full of tile T implies that
+    // P_{T-2} V_{T-2} has completed (S_T is issued after it), so the barrier is in phase T - 1 or T and the parity of
+    // T - 1 is unambiguous.  After the loop that argument no longer holds, hence the separate all_done barrier.
     float m = -INFINITY, l = 0.f, l_prev = 0.f;
     int g = 0, t = 0;
 #pragma unroll 1
     for (int T = 0; T < total; ++T) {
-      if (t == 0) { l_prev = l; l = 0.f; m = -INFINITY; }
+      const bool stage_q = t == 0 && g + 1 < kHeadsPerCta;
+      if (stage_q) load_q(g + 1);          // lands under this tile's softmax; stored after P below
+      if (t == 0) { l_prev = l; l = 0.f; }
       FY_AW(11, ptx::mbar_wait(&s_full[T & 1], (T >> 1) & 1))
       ptx::tc_fence_after();
       // the whole 64-key row is read: the other half only for the row maximum (no exchange, no barrier in the loop)
@@ -335,7 +345,7 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
 #pragma unroll
       for (int j = 0; j < HC; ++j) s[j] = __uint_as_float(sv[j]);
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-      if ((t + 1) * kBK > L) {
+      if ((t + 1) * kBK > L) {           // the head's last tile may be partial: keys >= L are masked
 #pragma unroll
         for (int j = 0; j < HC; ++j) {
           if (t * kBK + half * HC + j >= L) s[j] = -INFINITY;
@@ -347,17 +357,38 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       }
 #pragma unroll
       for (int j = 0; j < HC; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], s[j]);
-      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      const float m_new = fmaxf(m, mx * kLog2e);     // finite: every tile holds at least one valid key
-      const float corr = ex2(m - m_new);             // 0 on the first tile of a head (m = -inf)
-      m = m_new;
+      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * kLog2e;   // finite: >= 1 valid key
+      // Running maximum.  Both threads of a row see the same mx and take the same decisions.
+      if (t == 0) {
+        m = mx;                          // a head's first P V overwrites O: nothing to rescale
+      } else {
+        const bool need = mx > m + kRescaleSlack;
+        if (__any_sync(0xffffffffu, need)) {
+          // rare: rescale this thread's 32 O columns in tensor memory (P_{T-1} V_{T-1} must have landed)
+          FY_AW(12, ptx::mbar_wait(o_full, (T - 1) & 1))
+          ptx::tc_fence_after();
+          const float corr = need ? ex2(m - mx) : 1.0f;
+          uint32_t ov[32];
+          const uint32_t oa = t_row + kColO + (g & 1) * 64 + half * HC;
+          ptx::tmem_ld_32x32(oa, ov);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) sw[j] = __float_as_uint(__uint_as_float(ov[j]) * corr);
+          ptx::tmem_st_32x16(oa, reinterpret_cast<const uint32_t(&)[16]>(sw[0]));
+#pragma unroll
+          for (int j = 0; j < 16; ++j) sw[16 + j] = __float_as_uint(__uint_as_float(ov[16 + j]) * corr);
+          ptx::tmem_st_32x16(oa + 16, reinterpret_cast<const uint32_t(&)[16]>(sw[16]));
+          l *= corr;
+          if (need) m = mx;
+        }
+      }
       float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int j = 0; j < HC; ++j) {
-        s[j] = ex2(fmaf(s[j], kLog2e, -m_new));
+        s[j] = ex2(fmaf(s[j], kLog2e, -m));
         sum4[j & 3] += s[j];
       }
-      l = l * corr + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));   // partial (this half's keys)
+      l += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);   // partial (this half's keys); the halves are added at the end
       // P row -> tensor memory: keys [32 half, 32 half + 32) are columns [16 half, 16 half + 16) of the hi and of the
       // lo block of buffer T & 1 (two bf16 per column, even key in the low half-word)
       {
@@ -373,8 +404,9 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       }
       // Q of the next head goes into the buffer head g - 1 used: s_full of this tile implies every earlier product
       // (all S of head g - 1) has completed.
-      const bool stage_q = t == 0 && g + 1 < kHeadsPerCta;
       if (stage_q) store_q(g + 1);
+      const bool head_done = t == 0 && T > 0;           // head g - 1 is complete once P_{T-1} V_{T-1} has landed
+      if (head_done) FY_AW(12, ptx::mbar_wait(o_full, (T - 1) & 1))
       ptx::tmem_st_wait();
       ptx::tc_fence_before();
       __syncwarp();
@@ -382,21 +414,10 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
         ptx::mbar_arrive(&p_full[T & 1]);
         if (stage_q) ptx::mbar_arrive(&q_full[(g + 1) & 1]);
       }
-      if (stage_q && g + 2 < kHeadsPerCta) load_q(g + 2);
-      // Fold O_{T-1} (long finished: its MMA ran under this tile's softmax) into the running accumulator, one tile
-      // late so that the tensor-core latency of P V is never waited for; then rescale for this tile's maximum.
-      if (T > 0) fold_o(T - 1);
-      if (t == 0) {
-        if (T > 0) finish_head(g - 1, l_prev);
-#pragma unroll
-        for (int j = 0; j < HC; ++j) o[j] = 0.f;
-      } else {
-#pragma unroll
-        for (int j = 0; j < HC; ++j) o[j] *= corr;
-      }
+      if (head_done) finish_head(g - 1, l_prev);
       if (++t == nkt) { t = 0; ++g; }
     }
-    fold_o(total - 1);
+    ptx::mbar_wait(all_done, 0);
     finish_head(kHeadsPerCta - 1, l);
     FY_AP(if (threadIdx.x == 0) {
       for (int i = 11; i < 14; ++i) atomicAdd(&g_attn_stall[i], (unsigned long long)aw[i]);
