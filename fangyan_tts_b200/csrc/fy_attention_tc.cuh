@@ -6,20 +6,22 @@
 // Q is constant over a head's key tiles and P is produced by the softmax threads, so neither ever touches shared
 // memory -- the only operand bytes the shared-memory port serves are the K and V tiles (2 KB per MMA instead of 6 KB,
 // which is what held the all-shared-memory version at ~100 clk per M128 N64 K16 instruction against a 32 clk floor).
-//   warp 9, one thread : TMA loads of the K / V 64-key tiles (hi and lo halves) into a kStages ring
-//   warp 8, one thread : every tcgen05.mma
+//   warp 17, one thread: TMA loads of the K / V 64-key tiles (hi and lo halves) into a kStages ring
+//   warp 16 (one elected lane): every tcgen05.mma
 //                        S_t = Q K_t^T   (M 128, N 64, K 64; three products hi*hi + hi*lo + lo*hi)
 //                        O_t = P_t V_t   (M 128, N 64, K 64 keys; V is consumed MN-major, i.e. exactly as the
 //                                         [key][d] tile TMA delivers it -- no transpose anywhere)
 //                        O accumulates in TMEM over a head's tiles (two buffers, alternating by head).
-//   warps 0-7, 2 threads per query row (32 keys each): every thread reads the whole 64-key S row from TMEM for the row
-//                        maximum (no exchange, no barrier in the loop), exponentiates its 32 keys, packs
-//                        P = 2^(s log2e - m) to bf16 hi | lo and stores it to TMEM with tcgen05.st.  The running
-//                        maximum m only moves when the new one exceeds it by more than 2^8 (P stays <= 256, which the
-//                        hi | lo split carries exactly); only then is O rescaled in TMEM (tcgen05.ld / st of the
-//                        thread's 32 columns) -- about once per head instead of a read-back every tile.  The same
-//                        threads stage Q: each reads its 64 + 64 bytes of the next head's query row from global memory
-//                        a head ahead and stores them to TMEM under a first tile's softmax.
+//   warps 0-15, FOUR threads per query row (16 keys each; the role-stall counters showed the softmax warps to be
+//                        latency-bound at two warps per scheduler, and the four warps of a row quarter share one
+//                        scheduler, so waiting for each other costs no issue slots): tcgen05.ld of the thread's 16
+//                        scores, partial row maximum exchanged through shared memory (one 128-thread named barrier
+//                        per row quarter), P = 2^(s log2e - m) packed to bf16 hi | lo and stored to TMEM with
+//                        tcgen05.st.  The running maximum m only moves when the new one exceeds it by more than 2^8
+//                        (P stays <= 256, which the hi | lo split carries exactly); only then is O rescaled in TMEM
+//                        (tcgen05.ld / st of the thread's 16 columns) -- about once per head instead of a read-back
+//                        every tile.  The same threads stage Q: each reads its 32 + 32 bytes of the next head's query
+//                        row from global memory and stores them to TMEM under a first tile's softmax.
 // S, P, Q and O are double-buffered in TMEM (all 512 columns): S_{t+1} is computed while the softmax of tile t runs,
 // and a head is normalised and stored under the first products of the next head.
 // Rows past the utterance inside a tile belong to the next utterance or a guard row: keys are masked, queries are
@@ -32,13 +34,15 @@
 namespace fy {
 namespace attn_tc {
 
-constexpr int kBQ = 128, kBK = 64, kDH = 64, kThreads = 320, kStages = 4;
-constexpr int kSoftmaxThreads = 256;       // two threads per query row: keys / head-dim columns [0, 32) and [32, 64)
+constexpr int kBQ = 128, kBK = 64, kDH = 64, kStages = 4;
+constexpr int kParts = 4;                  // threads per query row: keys / head-dim columns [16 part, 16 part + 16)
+constexpr int kSoftmaxWarps = 4 * kParts, kSoftmaxThreads = 32 * kSoftmaxWarps;
+constexpr int kThreads = kSoftmaxThreads + 64;
 constexpr int kKVBytes = kBK * 128;        // one [64][64] bf16 tile
 constexpr int kStageBytes = 4 * kKVBytes;  // K hi, K lo, V hi, V lo
 constexpr int kHeadsPerCta = 4;           // heads walked by one CTA (launch, TMEM allocation, pipeline fill paid once)
 constexpr int kTileBytes = kStages * kStageBytes;
-constexpr int kCtrlBytes = 256 + 2 * 2 * kBQ * 4;      // barriers + TMEM holder, then the row max / sum exchange
+constexpr int kCtrlBytes = 256 + 2 * 2 * kParts * kBQ * 4;   // barriers + TMEM holder, then the row max and sum exchange
 constexpr int kSmemBytes = kTileBytes + kCtrlBytes + 1024;   // > half an SM's shared memory: one CTA per SM (TMEM is whole)
 constexpr int kAlignSlack = 1024;
 static_assert(kSmemBytes > 114 * 1024 && kSmemBytes <= 227 * 1024, "shared memory budget");
@@ -106,7 +110,8 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
   uint64_t* all_done = s_full + 11;           // 1    every product of the CTA has completed
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(s_full + 12);
   static_assert((4 * kStages + 13) * 8 <= 256, "barrier block");
-  float* xch = reinterpret_cast<float*>(bars + 32);   // [2 (tile parity)][2 (half)][128 rows]: row max / row sum exchange
+  float* xmax = reinterpret_cast<float*>(bars + 32);   // [2 (tile parity)][kParts][128 rows]: partial row maxima
+  float* xsum = xmax + 2 * kParts * kBQ;               // [2 (head parity)][kParts][128 rows]: partial row sums
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int2 tl = p.tiles[blockIdx.x];
@@ -115,6 +120,28 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
   const int P = p.utt_P[u], L = p.utt_L[u];
   const int nkt = (L + kBK - 1) / kBK;
   const int total = nkt * kHeadsPerCta;            // global tile index T = g * nkt + t: every ring / parity is keyed on T
+
+  // Softmax threads: four per query row (warps w, w+4, w+8, w+12 own row quarter w).  Q staging: a thread owns head-dim
+  // values [16 part, 16 part + 16) of its query row, hi and lo halves; the first head's loads are issued here so that
+  // they land under the barrier initialisation and the TMEM allocation.
+  const int wq = warp & 3, part = warp >> 2;
+  const int row = wq * 32 + lane;
+  constexpr int PC = kBK / kParts;     // 16 keys (and 16 head-dim columns) per thread
+  const bool q_row_ok = warp < kSoftmaxWarps && P + q0 + row < p.rows;
+  const __nv_bfloat16* q_src = p.q + (size_t)(q_row_ok ? P + q0 + row : 0) * p.ld + h0 * kDH + (part & 3) * PC;
+  uint32_t qh[8], ql[8];
+  auto load_q = [&](int g) {
+    const uint4* a = reinterpret_cast<const uint4*>(q_src + g * kDH);
+    const uint4* b = reinterpret_cast<const uint4*>(q_src + g * kDH + p.lo_off);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const uint4 x = q_row_ok ? __ldg(a + c) : make_uint4(0u, 0u, 0u, 0u);
+      const uint4 y = q_row_ok ? __ldg(b + c) : make_uint4(0u, 0u, 0u, 0u);
+      qh[4 * c] = x.x; qh[4 * c + 1] = x.y; qh[4 * c + 2] = x.z; qh[4 * c + 3] = x.w;
+      ql[4 * c] = y.x; ql[4 * c + 1] = y.y; ql[4 * c + 2] = y.z; ql[4 * c + 3] = y.w;
+    }
+  };
+  if (warp < kSoftmaxWarps) load_q(0);
 
   if (threadIdx.x == kSoftmaxThreads) {
     ptx::prefetch_tmap(&p.tm_kv);
@@ -127,12 +154,12 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&s_full[i], 1);
-      ptx::mbar_init(&s_empty[i], 8);
-      ptx::mbar_init(&p_full[i], 8);
-      ptx::mbar_init(&q_full[i], 8);
+      ptx::mbar_init(&s_empty[i], kSoftmaxWarps);
+      ptx::mbar_init(&p_full[i], kSoftmaxWarps);
+      ptx::mbar_init(&q_full[i], kSoftmaxWarps);
     }
-    ptx::mbar_init(&o_empty[0], 8);
-    ptx::mbar_init(&o_empty[1], 8);
+    ptx::mbar_init(&o_empty[0], kSoftmaxWarps);
+    ptx::mbar_init(&o_empty[1], kSoftmaxWarps);
     ptx::mbar_init(o_full, 1);
     ptx::mbar_init(all_done, 1);
     ptx::fence_mbar_init();
@@ -143,7 +170,7 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_holder;
 
-  if (warp == 9) {
+  if (warp == kSoftmaxWarps + 1) {
     if (lane == 0) {
       // ------------------------------------------------ TMA producer: K / V tiles (ring)
       FY_AP(long long aw[16] = {0}; const long long aw_t0 = clock64();)
@@ -165,7 +192,7 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       FY_AP(for (int i = 0; i < 3; ++i) atomicAdd(&g_attn_stall[i], (unsigned long long)aw[i]);
             atomicAdd(&g_attn_stall[3], (unsigned long long)(clock64() - aw_t0));)
     }
-  } else if (warp == 8) {
+  } else if (warp == kSoftmaxWarps) {
     {
       // ------------------------------------------------ every MMA.  The whole warp runs this loop (waits included) and
       // one elected lane issues each instruction: see ptx::mma_bf16_ts_elect.
@@ -240,60 +267,41 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       })
     }
   } else {
-    // ------------------------------------------------ softmax: two threads per query row (warps w and w + 4)
-    const int wq = warp & 3, half = warp >> 2;
-    const int row = wq * 32 + lane;
+    // ------------------------------------------------ softmax: four threads per query row (warps w, w+4, w+8, w+12)
     const uint32_t t_row = tmem + (static_cast<uint32_t>(wq * 32) << 16);
     const float kLog2e = 1.4426950408889634f;
-    constexpr int HC = kBK / 2;     // 32 keys (and 32 head-dim columns) per thread
     FY_AP(long long aw[16] = {0}; const long long aw_t0 = clock64();)
-    // Q staging: this thread owns head-dim values [32 half, 32 half + 32) of its query row, hi and lo halves
-    const bool q_row_ok = P + q0 + row < p.rows;
-    const __nv_bfloat16* q_src = p.q + (size_t)(q_row_ok ? P + q0 + row : 0) * p.ld + h0 * kDH + half * HC;
-    uint32_t qh[16], ql[16];
-    auto load_q = [&](int g) {
-      const uint4* a = reinterpret_cast<const uint4*>(q_src + g * kDH);
-      const uint4* b = reinterpret_cast<const uint4*>(q_src + g * kDH + p.lo_off);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const uint4 x = q_row_ok ? __ldg(a + c) : make_uint4(0u, 0u, 0u, 0u);
-        const uint4 y = q_row_ok ? __ldg(b + c) : make_uint4(0u, 0u, 0u, 0u);
-        qh[4 * c] = x.x; qh[4 * c + 1] = x.y; qh[4 * c + 2] = x.z; qh[4 * c + 3] = x.w;
-        ql[4 * c] = y.x; ql[4 * c + 1] = y.y; ql[4 * c + 2] = y.z; ql[4 * c + 3] = y.w;
-      }
-    };
     auto store_q = [&](int g) {   // followed by tmem_st_wait + arrive by the caller
-      const uint32_t qa = t_row + kColQ + (g & 1) * 64 + half * 16;
-      ptx::tmem_st_32x16(qa, qh);
-      ptx::tmem_st_32x16(qa + 32, ql);
+      const uint32_t qa = t_row + kColQ + (g & 1) * 64 + part * 8;
+      ptx::tmem_st_32x8(qa, qh);
+      ptx::tmem_st_32x8(qa + 32, ql);
     };
-    load_q(0);
-    store_q(0);
+    store_q(0);                            // loaded before the prologue barrier
     ptx::tmem_st_wait();
     ptx::tc_fence_before();
     __syncwarp();
     if (lane == 0) ptx::mbar_arrive(&q_full[0]);
-    // Head epilogue (the caller has waited for the head's last P V): read this thread's 32 O columns, add the two
-    // halves' row sums (exchanged through shared memory between warps w and w + 4 only: named barrier 1 + wq,
-    // 64 threads), normalise, split to bf16 hi | lo and store.
+    // Head epilogue (the caller has waited for the head's last P V): read this thread's 16 O columns, add the four
+    // partial row sums (shared memory + the row quarter's named barrier 1 + wq, 128 threads), normalise, split to
+    // bf16 hi | lo and store.
     auto finish_head = [&](int g, float l) {
-      const int col = (h0 + g) * kDH + half * HC;
+      const int col = (h0 + g) * kDH + part * PC;
       ptx::tc_fence_after();
-      uint32_t ov[32];
-      ptx::tmem_ld_32x32(t_row + kColO + (g & 1) * 64 + half * HC, ov);
+      uint32_t ov[16];
+      ptx::tmem_ld_32x16(t_row + kColO + (g & 1) * 64 + part * PC, ov);
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&o_empty[g & 1]);
-      float* xl = xch + (g & 1) * 2 * kBQ;   // slot g & 1: its next use is two pair barriers away
-      xl[half * kBQ + row] = l;
-      FY_AW(13, asm volatile("bar.sync %0, 64;\n" ::"r"(1 + wq) : "memory"))
-      l += xl[(half ^ 1) * kBQ + row];
+      float* xl = xsum + (g & 1) * kParts * kBQ;   // slot g & 1: its next use is two barriers away
+      xl[part * kBQ + row] = l;
+      FY_AW(13, asm volatile("bar.sync %0, 128;\n" ::"r"(1 + wq) : "memory"))
+      const float lt = (xl[row] + xl[kBQ + row]) + (xl[2 * kBQ + row] + xl[3 * kBQ + row]);
       if (q0 + row < L) {
-        const float inv = 1.0f / l;
+        const float inv = 1.0f / lt;
         __nv_bfloat16* dst = p.out + (size_t)(P + q0 + row) * p.ld + col;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           float a[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) a[j] = __uint_as_float(ov[8 * c + j]) * inv;
@@ -312,7 +320,7 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       if (q0 + row == L || (row == kBQ - 1 && q0 + kBQ == L)) {
         __nv_bfloat16* dst = p.out + (size_t)(P + L) * p.ld + col;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           *reinterpret_cast<uint4*>(dst + 8 * c) = make_uint4(0u, 0u, 0u, 0u);
           *reinterpret_cast<uint4*>(dst + p.lo_off + 8 * c) = make_uint4(0u, 0u, 0u, 0u);
         }
@@ -333,74 +341,69 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       if (t == 0) { l_prev = l; l = 0.f; }
       FY_AW(11, ptx::mbar_wait(&s_full[T & 1], (T >> 1) & 1))
       ptx::tc_fence_after();
-      // the whole 64-key row is read: the other half only for the row maximum (no exchange, no barrier in the loop)
-      uint32_t sv[32], sw[32];
-      ptx::tmem_ld_32x32(t_row + (T & 1) * kBK + (half ^ 1) * HC, sw);
-      ptx::tmem_ld_32x32(t_row + (T & 1) * kBK + half * HC, sv);
+      uint32_t sv[16];
+      ptx::tmem_ld_32x16(t_row + (T & 1) * kBK + part * PC, sv);
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&s_empty[T & 1]);
-      float s[HC];
+      float s[PC];
 #pragma unroll
-      for (int j = 0; j < HC; ++j) s[j] = __uint_as_float(sv[j]);
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      for (int j = 0; j < PC; ++j) s[j] = __uint_as_float(sv[j]);
       if ((t + 1) * kBK > L) {           // the head's last tile may be partial: keys >= L are masked
 #pragma unroll
-        for (int j = 0; j < HC; ++j) {
-          if (t * kBK + half * HC + j >= L) s[j] = -INFINITY;
-          if (t * kBK + (half ^ 1) * HC + j < L) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(sw[j]));
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < HC; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(sw[j]));
+        for (int j = 0; j < PC; ++j)
+          if (t * kBK + part * PC + j >= L) s[j] = -INFINITY;
       }
+      float mx4[4];
 #pragma unroll
-      for (int j = 0; j < HC; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], s[j]);
-      const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * kLog2e;   // finite: >= 1 valid key
-      // Running maximum.  Both threads of a row see the same mx and take the same decisions.
+      for (int j = 0; j < 4; ++j) mx4[j] = fmaxf(fmaxf(s[j], s[4 + j]), fmaxf(s[8 + j], s[12 + j]));
+      // row maximum over the four parts: slot T & 1 of the exchange buffer (its next use is two barriers away)
+      float* xm = xmax + (T & 1) * kParts * kBQ;
+      xm[part * kBQ + row] = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      FY_AW(13, asm volatile("bar.sync %0, 128;\n" ::"r"(1 + wq) : "memory"))
+      const float mx = fmaxf(fmaxf(xm[row], xm[kBQ + row]), fmaxf(xm[2 * kBQ + row], xm[3 * kBQ + row])) * kLog2e;
+      // Running maximum (finite: every tile holds a valid key).  The four threads of a row see the same mx and take
+      // the same decisions.
       if (t == 0) {
         m = mx;                          // a head's first P V overwrites O: nothing to rescale
       } else {
         const bool need = mx > m + kRescaleSlack;
         if (__any_sync(0xffffffffu, need)) {
-          // rare: rescale this thread's 32 O columns in tensor memory (P_{T-1} V_{T-1} must have landed)
+          // rare: rescale this thread's 16 O columns in tensor memory (P_{T-1} V_{T-1} must have landed)
           FY_AW(12, ptx::mbar_wait(o_full, (T - 1) & 1))
           ptx::tc_fence_after();
           const float corr = need ? ex2(m - mx) : 1.0f;
-          uint32_t ov[32];
-          const uint32_t oa = t_row + kColO + (g & 1) * 64 + half * HC;
-          ptx::tmem_ld_32x32(oa, ov);
+          uint32_t ov[16];
+          const uint32_t oa = t_row + kColO + (g & 1) * 64 + part * PC;
+          ptx::tmem_ld_32x16(oa, ov);
           ptx::tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 16; ++j) sw[j] = __float_as_uint(__uint_as_float(ov[j]) * corr);
-          ptx::tmem_st_32x16(oa, reinterpret_cast<const uint32_t(&)[16]>(sw[0]));
-#pragma unroll
-          for (int j = 0; j < 16; ++j) sw[16 + j] = __float_as_uint(__uint_as_float(ov[16 + j]) * corr);
-          ptx::tmem_st_32x16(oa + 16, reinterpret_cast<const uint32_t(&)[16]>(sw[16]));
+          for (int j = 0; j < 16; ++j) ov[j] = __float_as_uint(__uint_as_float(ov[j]) * corr);
+          ptx::tmem_st_32x16(oa, ov);
           l *= corr;
           if (need) m = mx;
         }
       }
       float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int j = 0; j < HC; ++j) {
+      for (int j = 0; j < PC; ++j) {
         s[j] = ex2(fmaf(s[j], kLog2e, -m));
         sum4[j & 3] += s[j];
       }
-      l += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);   // partial (this half's keys); the halves are added at the end
-      // P row -> tensor memory: keys [32 half, 32 half + 32) are columns [16 half, 16 half + 16) of the hi and of the
-      // lo block of buffer T & 1 (two bf16 per column, even key in the low half-word)
+      l += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);   // partial (this thread's keys); added up in finish_head
+      // P row -> tensor memory: keys [16 part, 16 part + 16) are columns [8 part, 8 part + 8) of the hi and of the lo
+      // block of buffer T & 1 (two bf16 per column, even key in the low half-word)
       {
-        uint32_t ph[16], pl[16];
+        uint32_t ph[8], pl[8];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
+        for (int j = 0; j < 8; ++j) {
           ph[j] = pack2(s[2 * j], s[2 * j + 1]);
           pl[j] = pack_lo(ph[j], s[2 * j], s[2 * j + 1]);
         }
-        const uint32_t pa = t_row + kColP + (T & 1) * 64 + half * 16;
-        ptx::tmem_st_32x16(pa, ph);
-        ptx::tmem_st_32x16(pa + 32, pl);
+        const uint32_t pa = t_row + kColP + (T & 1) * 64 + part * 8;
+        ptx::tmem_st_32x8(pa, ph);
+        ptx::tmem_st_32x8(pa + 32, pl);
       }
       // Q of the next head goes into the buffer head g - 1 used: s_full of this tile implies every earlier product
       // (all S of head g - 1) has completed.
