@@ -52,6 +52,7 @@ static_assert(kSmemBytes > 114 * 1024 && kSmemBytes <= 227 * 1024, "shared memor
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kColO = 128, kColP = 256, kColQ = 384;
 constexpr float kRescaleSlack = 8.0f;      // log2 units the running maximum may lag behind before O is rescaled
+                                           // (Params::slack; FY_ATTN_SLACK=0 forces the rescale path in tests)
 
 // kind::f16 instruction descriptor, bf16 A (K-major) x bf16 B, fp32 D; b_mn = 1: B is MN-major.
 __host__ __device__ constexpr uint32_t idesc(uint32_t m, uint32_t n, uint32_t b_mn) {
@@ -77,6 +78,7 @@ struct Params {
   const __nv_bfloat16* q;
   __nv_bfloat16* out;
   int ld, lo_off, rows;
+  float slack;         // kRescaleSlack
   const int2* tiles;   // (utterance, q0) per blockIdx.x, q0 a multiple of 128
   const int* utt_P;
   const int* utt_L;
@@ -368,7 +370,7 @@ __global__ void __launch_bounds__(kThreads, 1) attention_tc_kernel(const __grid_
       if (t == 0) {
         m = mx;                          // a head's first P V overwrites O: nothing to rescale
       } else {
-        const bool need = mx > m + kRescaleSlack;
+        const bool need = mx > m + p.slack;
         if (__any_sync(0xffffffffu, need)) {
           // rare: rescale this thread's 16 O columns in tensor memory (P_{T-1} V_{T-1} must have landed)
           FY_AW(12, ptx::mbar_wait(o_full, (T - 1) & 1))

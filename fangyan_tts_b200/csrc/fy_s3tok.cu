@@ -446,6 +446,8 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
     FY_TRY(make_tmap_bf16(&tc_params.tm_kv, b_k, Rtok, D * W, D * W, 64));
     FY_TRY(make_tmap_bf16(&tc_params.tm_v, b_v, Rtok, D * W, D * W, 64));
     tc_params.q = b_q; tc_params.out = b_att; tc_params.ld = D * W; tc_params.lo_off = D; tc_params.rows = Rtok;
+    static const float attn_slack = [] { const char* e = getenv("FY_ATTN_SLACK"); return e ? (float)atof(e) : attn_tc::kRescaleSlack; }();
+    tc_params.slack = attn_slack;
     tc_params.tiles = reinterpret_cast<const int2*>(d_meta + lay.m_tiles128);
     tc_params.utt_P = d_P; tc_params.utt_L = d_L;
   }

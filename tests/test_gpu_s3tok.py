@@ -100,8 +100,10 @@ def test_both_attention_kernels_agree():
 
     root = str(Path(__file__).resolve().parent.parent)
     out = {}
-    for v in ("1", "0"):
-        env = dict(os.environ, FY_ATTN_TC=v)
+    for v in ("1", "0", "slack0"):
+        # "slack0": tcgen05 kernel with no slack on the running maximum, i.e. O is rescaled in tensor memory whenever a
+        # tile raises the row maximum (the default 2^8 slack makes that path rare)
+        env = dict(os.environ, FY_ATTN_TC="1", FY_ATTN_SLACK="0") if v == "slack0" else dict(os.environ, FY_ATTN_TC=v)
         r = subprocess.run([sys.executable, "-c", _ALT_ATTENTION, root], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
         out[v] = json.loads(r.stdout.strip().splitlines()[-1])
@@ -111,3 +113,7 @@ def test_both_attention_kernels_agree():
     assert float(np.abs(a - b).max()) <= 2e-4
     ta, tb = np.asarray(out["1"]["tok"]), np.asarray(out["0"]["tok"])
     assert float((ta == tb).mean()) >= 0.999
+    c = np.asarray(out["slack0"]["pre"])
+    assert out["slack0"]["counts"] == out["1"]["counts"] and np.isfinite(c).all()
+    assert float(np.abs(a - c).max()) <= 2e-4
+    assert float((np.asarray(out["slack0"]["tok"]) == ta).mean()) >= 0.999
