@@ -1,5 +1,5 @@
 #!/usr/bin/env python3
-"""Where do the tcgen05 attention roles wait?  (FY_ATTN_TC=1)  Needs the debug build:
+"""Where do the tcgen05 attention roles wait?  Needs the debug build:
     FY_BUILD_TAG=prof FY_NVCC_EXTRA=-DFY_STALLPROF python -m fangyan_tts_b200.build
 Runs one device-resident stage-2 step and prints the share of each role's lifetime spent blocked on each barrier."""
 import ctypes as C
@@ -41,10 +41,10 @@ def main():
     n = max(v[15], 1)
     pl, il, sl = max(v[3], 1), max(v[10], 1), max(v[14], 1)
     print("CTAs*launches=%d  life/CTA: producer %.1f issuer %.1f softmax %.1f kclk" % (n, pl / n / 1e3, il / n / 1e3, sl / n / 1e3))
-    print("producer: k_empty %.1f%% v_empty %.1f%% q_empty %.1f%%" % tuple(100.0 * v[i] / pl for i in (0, 1, 2)))
+    print("producer: k_empty %.1f%% v_empty %.1f%%" % tuple(100.0 * v[i] / pl for i in (0, 1)))
     print("issuer  : k_full %.1f%% s_empty %.1f%% v_full %.1f%% p_full %.1f%% o_empty %.1f%% q_full %.1f%%" % tuple(
         100.0 * v[i] / il for i in (4, 5, 6, 7, 8, 9)))
-    print("softmax : s_full %.1f%% o_full %.1f%% bar.sync %.1f%%" % tuple(100.0 * v[i] / sl for i in (11, 12, 13)))
+    print("softmax (thread 0): s_full %.1f%% o_full %.1f%% bar.sync %.1f%%" % tuple(100.0 * v[i] / sl for i in (11, 12, 13)))
 
 
 if __name__ == "__main__":
