@@ -99,7 +99,7 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
     from .audio_io import read_wav
     from .configs import campplus_config, s3_config
     from .engine import Engine, kaldi_num_frames
-    from .pipeline import Extractor, Utt, plan_batches, shard_indices
+    from .pipeline import Extractor, Utt, plan_batches, shard_indices, split_tokens
     from .weights import load_state
 
     env = _dist_env()
@@ -119,20 +119,46 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         eng.load_s3tok(state, s3_config())
     del state
 
+    t_weights = time.perf_counter() - t_start
     utt2wav = kaldi_io.read_table(os.path.join(args.dir, "wav.scp"))
     keys, paths = list(utt2wav.keys()), list(utt2wav.values())
     pool = ThreadPoolExecutor(max_workers=max(1, args.num_thread))
+    t0 = time.perf_counter()
     heads = scan_durations(keys, paths, pool)
     n16 = [len16k(fr, sr) for fr, _, sr in heads]
     dur = [n / SR for n in n16]
     mine = shard_indices(dur, rank, world)
+    t_scan = time.perf_counter() - t0
     ex = Extractor(eng, float(os.environ.get("FY_BATCH_SECONDS", "2400")), int(os.environ.get("FY_BATCH_UTTS", "4096")))
     dev = eng.device
+    tm = {"decode_wait_s": 0.0, "gpu_events": []}
 
     def load_one(i):
         x, sr = read_wav(paths[i], keys[i])
         return Utt(x, sr)
 
+    def batches_of(todo):
+        """(indices, decoded utterances) per batch; the time this rank's main thread spends blocked on the reader pool
+        is accumulated in tm (the GPU keeps running the previous batch meanwhile: nothing in the loop synchronises)."""
+        local_dur = [dur[i] for i in todo]
+        plan = [[todo[j] for j in b] for b in plan_batches(local_dur, ex.max_batch_seconds, ex.max_batch_utts)]
+        it = iter(_progress(prefetch(plan, load_one, pool), len(plan), rank, f"stage {stage}"))
+        while True:
+            t = time.perf_counter()
+            item = next(it, None)
+            tm["decode_wait_s"] += time.perf_counter() - t
+            if item is None:
+                return
+            a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            yield item
+            z.record()
+            tm["gpu_events"].append((a, z))
+
+    def to_dev(values, dtype):
+        return torch.from_numpy(np.asarray(values, dtype=dtype)).to(dev, non_blocking=True)
+
+    t_loop = time.perf_counter()
     if stage == 1:
         utt2spk = kaldi_io.read_table(os.path.join(args.dir, "utt2spk"))
         missing = [k for k in keys if k not in utt2spk]
@@ -140,64 +166,73 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
             raise KeyError(f"utt2spk lacks {len(missing)} utterances of wav.scp, e.g. {missing[:3]}")
         spk_names = list(dict.fromkeys(utt2spk[k] for k in keys))
         spk_index = {s: j for j, s in enumerate(spk_names)}
+        spk_of = np.fromiter((spk_index[utt2spk[k]] for k in keys), dtype=np.int32, count=len(keys))
         for i in mine:
             if kaldi_num_frames(n16[i]) < 3:
                 raise ValueError(f"utterance {keys[i]}: {n16[i]} samples at 16 kHz is too short for a speaker embedding")
-        local_dur = [dur[i] for i in mine]
-        batches = [[mine[j] for j in b] for b in plan_batches(local_dur, ex.max_batch_seconds, ex.max_batch_utts)]
         ssum = torch.zeros(len(spk_names), 192, device=dev)
         scnt = torch.zeros(len(spk_names), dtype=torch.int32, device=dev)
-        idx_parts, emb_parts = [], []
-        for b, utts in _progress(prefetch(batches, load_one, pool), len(batches), rank, "stage 1"):
+        order, emb_parts = [], []
+        for b, utts in batches_of(mine):
             emb = ex.embed_batch(utts)
-            spk = torch.tensor([spk_index[utt2spk[keys[i]]] for i in b], dtype=torch.int32, device=dev)
-            eng.speaker_sum(emb, spk, len(spk_names), ssum, scnt)
-            idx_parts.append(torch.tensor(b, dtype=torch.int64, device=dev))
+            eng.speaker_sum(emb, to_dev(spk_of[b], np.int32), len(spk_names), ssum, scnt)
+            order.extend(b)
             emb_parts.append(emb)
-        index = torch.cat(idx_parts) if idx_parts else torch.zeros(0, dtype=torch.int64, device=dev)
+        index = to_dev(order, np.int64)
         emb = torch.cat(emb_parts) if emb_parts else torch.zeros(0, 192, device=dev)
+        torch.cuda.synchronize()
+        t_loop = time.perf_counter() - t_loop
+        t0 = time.perf_counter()
         full = D.gather_stage1(index, emb, len(keys))
         D.reduce_speakers(ssum, scnt)
         mean = eng.speaker_mean(ssum, scnt)
+        torch.cuda.synchronize()
+        t_gather = time.perf_counter() - t0
+        t0 = time.perf_counter()
         if rank == 0:
-            kaldi_io.save_atomic(kaldi_io.embeddings_to_dict(keys, full.cpu().numpy()),
-                                 os.path.join(args.dir, "utt2embedding.pt"))
-            kaldi_io.save_atomic(kaldi_io.speaker_dict(spk_names, mean.cpu().numpy()),
-                                 os.path.join(args.dir, "spk2embedding.pt"))
+            full_h, mean_h = full.cpu().numpy(), mean.cpu().numpy()          # one device-to-host copy each
+            kaldi_io.save_atomic(kaldi_io.embeddings_to_dict(keys, full_h), os.path.join(args.dir, "utt2embedding.pt"))
+            kaldi_io.save_atomic(kaldi_io.speaker_dict(spk_names, mean_h), os.path.join(args.dir, "spk2embedding.pt"))
             if os.environ.get("FY_SIDECAR", "1") != "0":      # compact copies for the Arrow stage-3 fast path
-                parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.EMB_SIDECAR), keys,
-                                                     full.cpu().numpy())
-                parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.SPK_SIDECAR), spk_names,
-                                                     mean.cpu().numpy())
+                parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.EMB_SIDECAR), keys, full_h)
+                parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.SPK_SIDECAR), spk_names, mean_h)
+        t_save = time.perf_counter() - t0
     else:
         gated = [i for i in mine if n16[i] / SR > 30]          # extract_speech_token.py:34-36: key kept, value []
         for i in gated:
             logging.warning("do not support extract speech token for audio longer than 30s (%s)", keys[i])
         todo = [i for i in mine if not n16[i] / SR > 30 and n16[i] >= 160]
-        local_dur = [dur[i] for i in todo]
-        batches = [[todo[j] for j in b] for b in plan_batches(local_dur, ex.max_batch_seconds, ex.max_batch_utts)]
-        idx_parts, cnt_parts, tok_parts = [], [], []
-        for b, utts in _progress(prefetch(batches, load_one, pool), len(batches), rank, "stage 2"):
+        order, cnt_all, tok_parts = [], [], []
+        for b, utts in batches_of(todo):
             tok, counts = ex.tokenize_batch(utts)
-            idx_parts.append(torch.tensor(b, dtype=torch.int64, device=dev))
-            cnt_parts.append(torch.tensor(counts, dtype=torch.int64, device=dev))
+            order.extend(b)
+            cnt_all.extend(counts)
             tok_parts.append(tok)
-        z = torch.zeros(0, dtype=torch.int64, device=dev)
-        index = torch.cat(idx_parts) if idx_parts else z
-        counts = torch.cat(cnt_parts) if cnt_parts else z
+        index, counts = to_dev(order, np.int64), to_dev(cnt_all, np.int64)
         toks = torch.cat(tok_parts) if tok_parts else torch.zeros(0, dtype=torch.int32, device=dev)
-        _, per_utt = D.gather_stage2(index, counts, toks, len(keys))
+        torch.cuda.synchronize()
+        t_loop = time.perf_counter() - t_loop
+        t0 = time.perf_counter()
+        full_cnt, flat = D.gather_stage2(index, counts, toks, len(keys))
+        torch.cuda.synchronize()
+        t_gather = time.perf_counter() - t0
+        t0 = time.perf_counter()
         if rank == 0:
-            out = {k: ([] if p is None else p.cpu().tolist()) for k, p in zip(keys, per_utt)}
-            kaldi_io.save_atomic(out, os.path.join(args.dir, "utt2speech_token.pt"))
+            cnt_h, flat_h = full_cnt.cpu().numpy(), flat.cpu().numpy()       # one device-to-host copy each
+            kaldi_io.save_atomic(dict(zip(keys, split_tokens(flat_h, cnt_h))), os.path.join(args.dir, "utt2speech_token.pt"))
             if os.environ.get("FY_SIDECAR", "1") != "0":
-                parquet_pack.write_token_sidecar(os.path.join(args.dir, parquet_pack.TOK_SIDECAR), keys,
-                                                 [None if p is None else p.cpu().numpy() for p in per_utt])
-    torch.cuda.synchronize()
+                parquet_pack.write_token_sidecar_flat(os.path.join(args.dir, parquet_pack.TOK_SIDECAR), keys, flat_h, cnt_h)
+        t_save = time.perf_counter() - t0
     if rank == 0:
         wall = time.perf_counter() - t_start
-        sys.stderr.write(json.dumps({"stage": stage, "utts": len(keys), "audio_hours": sum(dur) / 3600.0, "gpus": world,
-                                     "wall_s": wall, "precision": eng.precision}) + "\n")
+        gpu_s = sum(a.elapsed_time(z) for a, z in tm["gpu_events"]) / 1e3
+        sys.stderr.write(json.dumps({
+            "stage": stage, "utts": len(keys), "audio_hours": sum(dur) / 3600.0, "gpus": world, "wall_s": wall,
+            "precision": eng.precision, "audio_hours_per_s": sum(dur) / 3600.0 / wall,
+            # rank 0's view; decode+stage and GPU overlap inside loop_s (reader pool + upload ring run ahead of the kernels)
+            "split_s": {"engine_and_weights": t_weights, "header_scan": t_scan, "loop": t_loop,
+                        "loop_decode_wait": tm["decode_wait_s"], "loop_pack_upload": ex.ring.pack_seconds,
+                        "loop_gpu_busy": gpu_s, "gather": t_gather, "tolist_save": t_save}}) + "\n")
     pool.shutdown()
     eng.close()
     if world > 1:

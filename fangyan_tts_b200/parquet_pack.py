@@ -55,6 +55,13 @@ def write_token_sidecar(path, keys: Sequence[str], tokens: Sequence[Optional[np.
     _save_npz_atomic(path, keys=np.asarray(list(keys), dtype=np.str_), flat=flat, offsets=off)
 
 
+def write_token_sidecar_flat(path, keys: Sequence[str], flat: np.ndarray, counts: np.ndarray) -> None:
+    """The same file from already-packed ids (wav.scp order) + per-utterance counts: no per-utterance work."""
+    off = np.zeros(len(counts) + 1, dtype=np.int64)
+    np.cumsum(np.asarray(counts, dtype=np.int64), out=off[1:])
+    _save_npz_atomic(path, keys=np.asarray(list(keys), dtype=np.str_), flat=np.asarray(flat, dtype=np.int32), offsets=off)
+
+
 class _Rows:
     """key -> row view over a matrix or a ragged flat array, from a sidecar or from the reference's .pt dict."""
 

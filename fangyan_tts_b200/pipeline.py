@@ -6,8 +6,9 @@ for a whole batch per launch sequence instead of one utterance per onnxruntime c
 from __future__ import annotations
 
 import math
+import time
 from dataclasses import dataclass
-from typing import List, Sequence
+from typing import List, Optional, Sequence
 
 import numpy as np
 import torch
@@ -41,18 +42,76 @@ def plan_batches(durations: Sequence[float], max_seconds: float, max_utts: int) 
     return batches
 
 
-def shard_indices(durations: Sequence[float], rank: int, world: int) -> List[int]:
-    """Deal utterances (longest first) to the currently lightest rank: equal audio per rank, no duplication
-    (unlike DistributedSampler, examples/grpo/cosyvoice2/infer_dataset.py:311, which pads by repeating samples)."""
+def shard_assignment(durations: Sequence[float], world: int) -> np.ndarray:
+    """rank_of[i] for every utterance: deal utterances (longest first) to the currently lightest rank -- equal audio per
+    rank, no duplication (unlike DistributedSampler, examples/grpo/cosyvoice2/infer_dataset.py:311, which pads by
+    repeating samples).  Deterministic, so every rank derives the whole job's layout without communicating."""
+    import heapq
     order = sorted(range(len(durations)), key=lambda i: -durations[i])
-    load = [0.0] * world
-    mine = []
+    heap = [(0.0, k) for k in range(world)]
+    rank_of = np.zeros(len(durations), dtype=np.int32)
     for i in order:
-        r = min(range(world), key=lambda k: (load[k], k))
-        load[r] += durations[i]
-        if r == rank:
-            mine.append(i)
-    return sorted(mine)
+        load, k = heapq.heappop(heap)
+        rank_of[i] = k
+        heapq.heappush(heap, (load + durations[i], k))
+    return rank_of
+
+
+def shard_indices(durations: Sequence[float], rank: int, world: int) -> List[int]:
+    """This rank's utterances under shard_assignment, in wav.scp order."""
+    return np.nonzero(shard_assignment(durations, world) == rank)[0].tolist()
+
+
+def split_tokens(flat: np.ndarray, counts: np.ndarray) -> List[List[int]]:
+    """Packed ids + per-utterance counts -> list of Python int lists (the reference's value type,
+    extract_speech_token.py:48).  One tolist() of the whole array, then list slices: no per-utterance numpy call."""
+    ids = flat.tolist()
+    out, o = [], 0
+    for n in counts.tolist():
+        out.append(ids[o:o + n])
+        o += n
+    return out
+
+
+class PinnedRing:
+    """Host->device staging of packed int16 PCM: `slots` pinned buffers used in turn, each guarded by the event recorded
+    after its last copy, so a slot is never rewritten while the DMA that reads it may still be queued (the copy runs on
+    a side stream under the previous batch's kernels; the caller's stream waits for it)."""
+
+    def __init__(self, device: torch.device, slots: int = 3):
+        self.device = device
+        self.slots: List[Optional[torch.Tensor]] = [None] * slots
+        self.events: List[Optional[torch.cuda.Event]] = [None] * slots
+        self.k = 0
+        self.stream: Optional[torch.cuda.Stream] = None
+        self.pack_seconds = 0.0
+
+    def upload(self, arrays: Sequence[np.ndarray], total: int) -> torch.Tensor:
+        """Concatenate 1-D int16 arrays into the next slot and start its copy; returns the device tensor, which the
+        current stream may use (it waits for the copy)."""
+        t0 = time.perf_counter()
+        if self.stream is None:
+            self.stream = torch.cuda.Stream(self.device)
+        i = self.k % len(self.slots)
+        self.k += 1
+        if self.events[i] is not None:
+            self.events[i].synchronize()             # the previous copy out of this slot has finished
+        if self.slots[i] is None or self.slots[i].numel() < total:
+            self.slots[i] = None
+            self.slots[i] = torch.empty(max(int(total * 1.25), 1 << 16), dtype=torch.int16).pin_memory()
+        pin = self.slots[i][:total]
+        if arrays:
+            np.concatenate(arrays, out=pin.numpy())
+        main = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self.stream):
+            dev = pin.to(self.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        self.events[i] = ev
+        main.wait_event(ev)
+        dev.record_stream(main)
+        self.pack_seconds += time.perf_counter() - t0
+        return dev
 
 
 class Extractor:
@@ -60,8 +119,7 @@ class Extractor:
         self.eng = engine
         self.max_batch_seconds = max_batch_seconds
         self.max_batch_utts = max_batch_utts
-        self._pin = None
-        self._copy_stream = None
+        self.ring = PinnedRing(engine.device)
         self._d2h_stream = None
         self._res = [(None, None), (None, None)]
 
@@ -69,21 +127,13 @@ class Extractor:
     def _to_device_16k(self, utts: Sequence[Utt], mono: str):
         """Returns (packed pcm on device (int16 or float32), lengths).  mono = 'first' (stage 1: kaldi.fbank takes
         channel 0, extract_embedding.py:29) or 'mean' (stage 2, extract_speech_token.py:32-33).
-        Fast path: everything 16 kHz mono int16 -> one pinned copy, int16 on the wire."""
+        Fast path: everything 16 kHz mono int16 -> one pinned copy on the upload ring, int16 on the wire."""
         dev = self.eng.device
         simple = all(u.sr == SR and u.samples.dtype == np.int16 and (u.samples.shape[1] == 1 or mono == "first")
                      for u in utts)
         if simple:
             lens = [u.samples.shape[0] for u in utts]
-            total = int(sum(lens))
-            if self._pin is None or self._pin.numel() < total:
-                self._pin = torch.empty(max(total, 1), dtype=torch.int16).pin_memory()
-            host = self._pin[:total].numpy()
-            o = 0
-            for u, n in zip(utts, lens):
-                host[o:o + n] = u.samples[:, 0]
-                o += n
-            return self._pin[:total].to(dev, non_blocking=True), lens
+            return self.ring.upload([u.samples[:, 0] for u in utts], int(sum(lens))), lens
         # general path: float32, resample per sample-rate group on the device, then channel handling
         out, lens = [None] * len(utts), [0] * len(utts)
         groups = {}
@@ -130,11 +180,18 @@ class Extractor:
         return out
 
     # ------------------------------------------------------------------ both stages, one upload
-    def extract(self, utts: Sequence[Utt]):
+    def extract(self, utts: Sequence[Utt], shard=None):
         """Stages 1 and 2 over the same utterances: (embeddings float32 [n, 192], token lists) on the host, original
         order.  16 kHz mono PCM16 input (what prepare_training_data.py writes) is uploaded once per batch as int16 and
         feeds both front-ends; results stay on the device until the last batch has been launched, so host staging of
-        batch k+1 overlaps the kernels of batch k.  Anything else takes the two single-stage paths."""
+        batch k+1 overlaps the kernels of batch k.  Anything else takes the two single-stage paths.
+
+        shard = (index, n_total): `utts` are this rank's share of an n_total-utterance job (index[j] = position of
+        utts[j] in the job, see shard_indices).  Results then stay on the device, are gathered to rank 0 over the
+        process group (distributed.gather_stage1/2) and only rank 0 returns (embeddings [n_total, 192], n_total token
+        lists); the other ranks return (None, None)."""
+        if shard is not None:
+            return self._extract_sharded(utts, shard[0], shard[1])
         fused = all(u.sr == SR and u.samples.dtype == np.int16 and u.samples.shape[1] == 1 and
                     u.samples.shape[0] / SR <= MAX_TOKEN_SECONDS and u.samples.shape[0] >= 400 for u in utts)
         if not fused:
@@ -143,14 +200,9 @@ class Extractor:
         batches = plan_batches(dur, self.max_batch_seconds, self.max_batch_utts)
         if len(batches[0]) > 2 * RAMP_UTTS:      # short ramp-up batch: the GPU starts after staging 48 clips, not 1,000
             batches[0:1] = [batches[0][:RAMP_UTTS], batches[0][RAMP_UTTS:]]
-        total = sum(u.samples.shape[0] for u in utts)
-        if self._pin is None or self._pin.numel() < total:
-            self._pin = torch.empty(max(total, 1), dtype=torch.int16).pin_memory()
-        host = self._pin.numpy()
         dev = self.eng.device
         main = torch.cuda.current_stream(dev)
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(dev)
+        if self._d2h_stream is None:
             self._d2h_stream = torch.cuda.Stream(dev)
         out = np.zeros((len(utts), 192), dtype=np.float32)
         toks: List[List[int]] = [[] for _ in utts]
@@ -166,20 +218,11 @@ class Extractor:
                 toks[i] = th[p:p + n].tolist()
                 p += n
 
-        pending, o = [], 0
+        pending = []
         for k, idx in enumerate(batches):
             lens = [utts[i].samples.shape[0] for i in idx]
-            b0 = o
-            for i, n in zip(idx, lens):
-                host[o:o + n] = utts[i].samples[:, 0]
-                o += n
-            # upload on a side stream: the copy of batch k+1 runs under the kernels of batch k
-            with torch.cuda.stream(self._copy_stream):
-                pcm = self._pin[b0:o].to(dev, non_blocking=True)
-                ready = torch.cuda.Event()
-                ready.record(self._copy_stream)
-            main.wait_event(ready)
-            pcm.record_stream(main)
+            # upload on the ring's side stream: the copy of batch k+1 runs under the kernels of batch k
+            pcm = self.ring.upload([utts[i].samples[:, 0] for i in idx], int(sum(lens)))
             feat, frames = self.eng.fbank_cmn(pcm, lens)
             emb = self.eng.campplus(feat, frames)
             mel, mframes = self.eng.logmel(pcm, lens)
@@ -202,6 +245,36 @@ class Extractor:
         for item in pending:
             finish(item)
         return out, toks
+
+    def _extract_sharded(self, utts: Sequence[Utt], index: Sequence[int], n_total: int):
+        from . import distributed as D
+        for u in utts:
+            if not (u.sr == SR and u.samples.dtype == np.int16 and u.samples.shape[1] == 1 and
+                    400 <= u.samples.shape[0] <= MAX_TOKEN_SECONDS * SR):
+                raise ValueError("sharded extract takes 16 kHz mono PCM16 clips of 25 ms .. 30 s (the CLIs handle the rest)")
+        dev = self.eng.device
+        dur = [u.samples.shape[0] / SR for u in utts]
+        order, emb_p, tok_p, cnt_p = [], [], [], []
+        for idx in plan_batches(dur, self.max_batch_seconds, self.max_batch_utts):
+            lens = [utts[i].samples.shape[0] for i in idx]
+            pcm = self.ring.upload([utts[i].samples[:, 0] for i in idx], int(sum(lens)))
+            feat, frames = self.eng.fbank_cmn(pcm, lens)
+            emb_p.append(self.eng.campplus(feat, frames))
+            mel, mframes = self.eng.logmel(pcm, lens)
+            tok, counts = self.eng.s3tok(mel, mframes)
+            tok_p.append(tok)
+            cnt_p.extend(counts)
+            order.extend(index[i] for i in idx)
+        gidx = torch.from_numpy(np.asarray(order, dtype=np.int64)).to(dev)
+        cnt = torch.from_numpy(np.asarray(cnt_p, dtype=np.int64)).to(dev)
+        emb = torch.cat(emb_p) if emb_p else torch.zeros(0, 192, device=dev)
+        tok = torch.cat(tok_p) if tok_p else torch.zeros(0, dtype=torch.int32, device=dev)
+        full = D.gather_stage1(gidx, emb, n_total)
+        counts_full, flat = D.gather_stage2(gidx, cnt, tok, n_total)
+        if full is None:
+            return None, None
+        emb_h = full.cpu().numpy()
+        return emb_h, split_tokens(flat.cpu().numpy(), counts_full.cpu().numpy())
 
     def _result_buffers(self, slot: int, n_emb: int, n_tok: int):
         """Pinned host buffers for one batch's results (grown on demand, reused across calls)."""

@@ -29,12 +29,21 @@ def _worker(rank, world, port, out_path):
     mine = shard_indices(dur, rank, world)
     idx = torch.tensor(mine, dtype=torch.int64)
     full = D.gather_stage1(idx, emb[idx], N)
-    cnt, per_utt = D.gather_stage2(idx, counts[idx], torch.cat([toks[i] for i in mine]), N)
+    cnt, flat = D.gather_stage2(idx, counts[idx], torch.cat([toks[i] for i in mine]), N)
     ssum = torch.zeros(S, 192).index_add_(0, spk[idx], emb[idx])
     scnt = torch.zeros(S, dtype=torch.int32).index_add_(0, spk[idx], torch.ones(len(mine), dtype=torch.int32))
     D.reduce_speakers(ssum, scnt)
+    local = torch.stack([D.checksum(idx, emb[idx]), D.checksum_ragged(idx, counts[idx], torch.cat([toks[i] for i in mine]))])
+    torch.distributed.all_reduce(local)
     if rank == 0:
-        torch.save({"emb": full, "cnt": cnt, "tok": [p for p in per_utt], "ssum": ssum, "scnt": scnt}, out_path)
+        assert full.shape == (N, 192) and cnt.shape == (N,)
+        everyone = torch.arange(N)
+        assert int(local[0]) == int(D.checksum(everyone, full))          # nothing dropped, duplicated or misplaced
+        assert int(local[1]) == int(D.checksum_ragged(everyone, cnt, flat))
+        torch.save({"emb": full, "cnt": cnt, "tok": list(torch.split(flat, cnt.tolist())), "ssum": ssum, "scnt": scnt},
+                   out_path)
+    else:
+        assert full is None and cnt is None and flat is None             # only rank 0 receives
     torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 
@@ -56,4 +65,7 @@ def test_gather_and_speaker_reduce_world2(tmp_path):
 def test_single_process_helpers_are_identity():
     t = torch.arange(6).view(3, 2)
     assert D.world() == 1 and D.rank() == 0
-    assert torch.equal(D.all_gather_rows(t)[0], t)
+    assert torch.equal(D.gather_rows([t])[0], t) and D.row_counts(3, t.device) == [3]
+    idx = torch.tensor([2, 0, 1])
+    full, flat = D.gather_stage2(idx, torch.tensor([1, 2, 3]), torch.tensor([9, 5, 6, 1, 2, 3], dtype=torch.int32), 4)
+    assert full.tolist() == [2, 3, 1, 0] and flat.tolist() == [5, 6, 1, 2, 3, 9]   # wav.scp order, ragged
