@@ -111,12 +111,14 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         D.init(rank, world, "nccl", port, torch.device("cuda", local_rank))
     t_start = time.perf_counter()
     eng = Engine(local_rank, os.environ.get("FY_PRECISION", "bf16x3"))
-    state = {k: torch.from_numpy(np.ascontiguousarray(v, dtype=np.float32)) for k, v in load_state(args.onnx_path).items()
-             if v.dtype.kind == "f"}
+    cfg = campplus_config() if stage == 1 else s3_config()
+    # .onnx files are mapped by graph topology (weights.py); .npz / .pt carry our tensor names
+    state = {k: np.ascontiguousarray(v, dtype=np.float32)
+             for k, v in load_state(args.onnx_path, "campplus" if stage == 1 else "s3tok", cfg).items() if v.dtype.kind == "f"}
     if stage == 1:
-        eng.load_campplus(state, campplus_config())
+        eng.load_campplus(state, cfg)
     else:
-        eng.load_s3tok(state, s3_config())
+        eng.load_s3tok(state, cfg)
     del state
 
     t_weights = time.perf_counter() - t_start

@@ -124,6 +124,8 @@ class Engine:
         return arr, keep
 
     def load_campplus(self, state: dict, cfg):
+        from .weights import check_shapes
+        check_shapes(state, "campplus", cfg)          # full shapes (the C loader checks element counts)
         arr, keep = self._tensor_table(state)
         c = FyCamConfig()
         c.feat_dim, c.embed_dim, c.fcm_channels = cfg.feat_dim, cfg.embed_dim, cfg.fcm_channels
@@ -134,6 +136,8 @@ class Engine:
         check(self.lib.fy_load_campplus(self.h, arr, len(state), C.byref(c)))
 
     def load_s3tok(self, state: dict, cfg):
+        from .weights import check_shapes
+        check_shapes(state, "s3tok", cfg)
         arr, keep = self._tensor_table(state)
         c = FyS3Config(cfg.n_mels, cfg.d_model, cfg.n_head, cfg.n_layer, cfg.d_ff, cfg.fsmn_kernel, cfg.fsq_dim,
                        cfg.rope_theta, cfg.ln_eps, cfg.fsq_scale)

@@ -27,12 +27,13 @@ class CosyVoiceFrontEndB200:
         self.engine = Engine(device, precision)
         self.device = self.engine.device
 
-        def tensors(path):
-            return {k: torch.from_numpy(np.ascontiguousarray(v, dtype=np.float32)) for k, v in load_state(path).items()
+        def tensors(path, kind, cfg):
+            return {k: np.ascontiguousarray(v, dtype=np.float32) for k, v in load_state(path, kind, cfg).items()
                     if v.dtype.kind == "f"}
 
-        self.engine.load_campplus(tensors(campplus_model), campplus_config())
-        self.engine.load_s3tok(tensors(speech_tokenizer_model), s3_config())
+        cam_cfg, s3_cfg = campplus_config(), s3_config()
+        self.engine.load_campplus(tensors(campplus_model, "campplus", cam_cfg), cam_cfg)
+        self.engine.load_s3tok(tensors(speech_tokenizer_model, "s3tok", s3_cfg), s3_cfg)
 
     def load_wav(self, wav, target_sr: int = SR, min_sr: int = SR) -> torch.Tensor:
         """file_utils.load_wav: float32 [N] mono at 16 kHz on the device."""

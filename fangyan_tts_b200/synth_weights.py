@@ -15,6 +15,23 @@ import numpy as np
 from .configs import CamPlusConfig, S3Config
 
 
+class _Shapes:
+    """Stand-in for the random generator that records shapes instead of drawing values (campplus_shapes / s3tok_shapes)."""
+
+    @staticmethod
+    def standard_normal(shape, dtype=None):
+        return np.broadcast_to(np.float32(0), shape if isinstance(shape, tuple) else (shape,))
+
+    @staticmethod
+    def random(n):
+        return np.broadcast_to(np.float32(0), (n,))
+
+
+class _ShapeDict(dict):
+    def __setitem__(self, k, v):
+        super().__setitem__(k, tuple(np.shape(v)))
+
+
 def _bn(out: Dict[str, np.ndarray], rng, name: str, n: int, affine: bool = True):
     out[name + ".running_mean"] = (rng.standard_normal(n) * 0.1).astype(np.float32)
     out[name + ".running_var"] = (0.5 + rng.random(n)).astype(np.float32)
@@ -30,10 +47,19 @@ def _conv(out, rng, name: str, shape, bias: bool = False, gain: float = 1.6):
         out[name + ".bias"] = (rng.standard_normal(shape[0]) * 0.1).astype(np.float32)
 
 
-def campplus_state(cfg: CamPlusConfig | None = None, seed: int = 1986) -> Dict[str, np.ndarray]:
+def campplus_shapes(cfg: CamPlusConfig | None = None) -> Dict[str, tuple]:
+    """{tensor name: full shape} of everything fy_load_campplus looks up."""
+    return dict(campplus_state(cfg, _shapes=True))
+
+
+def s3tok_shapes(cfg: S3Config | None = None) -> Dict[str, tuple]:
+    return dict(s3tok_state(cfg, _shapes=True))
+
+
+def campplus_state(cfg: CamPlusConfig | None = None, seed: int = 1986, _shapes: bool = False) -> Dict[str, np.ndarray]:
     cfg = cfg or CamPlusConfig()
-    rng = np.random.default_rng(seed)
-    o: Dict[str, np.ndarray] = {}
+    rng = _Shapes() if _shapes else np.random.default_rng(seed)
+    o: Dict[str, np.ndarray] = _ShapeDict() if _shapes else {}
     c = cfg.fcm_channels
     _conv(o, rng, "head.conv1", (c, 1, 3, 3))
     _bn(o, rng, "head.bn1", c)
@@ -76,10 +102,10 @@ def campplus_state(cfg: CamPlusConfig | None = None, seed: int = 1986) -> Dict[s
     return o
 
 
-def s3tok_state(cfg: S3Config | None = None, seed: int = 1986) -> Dict[str, np.ndarray]:
+def s3tok_state(cfg: S3Config | None = None, seed: int = 1986, _shapes: bool = False) -> Dict[str, np.ndarray]:
     cfg = cfg or S3Config()
-    rng = np.random.default_rng(seed)
-    o: Dict[str, np.ndarray] = {}
+    rng = _Shapes() if _shapes else np.random.default_rng(seed)
+    o: Dict[str, np.ndarray] = _ShapeDict() if _shapes else {}
     d, f = cfg.d_model, cfg.d_ff
 
     def lin(name, n_out, n_in, bias=True, gain=1.0, extra=()):

@@ -194,3 +194,27 @@ def test_frontend_twin(data_dir):
     ref = CP.embed_one(cam, F.cmn(F.kaldi_fbank(F.resample(w, 24000))))
     got = fe._extract_spk_embedding(str(d / "wav" / "stereo24.wav"))[0].cpu()
     assert float(torch.nn.functional.cosine_similarity(got, ref, dim=0)) >= 0.9999
+
+
+def test_twin_loads_exporter_style_onnx(data_dir, tmp_path):
+    """the real --onnx_path files carry neither our names nor our layouts.  Graphs written with the torch
+    exporter's conventions (tests/onnx_writer.py: BatchNorm folded into Conv, MatMul [in, out], foreign names) load
+    through the topology mapping and give the same embedding / tokens as the .npz state they were written from."""
+    import os
+    import onnx_writer as OW
+    from fangyan_tts_b200.frontend import CosyVoiceFrontEndB200
+    d, keys, utts, st = data_dir
+    s3_cfg = S3Config(n_layer=N_LAYER)
+    OW.write_campplus(tmp_path / "campplus.onnx", synth_weights.campplus_state(seed=11), CamPlusConfig())
+    OW.write_s3tok(tmp_path / "speech_tokenizer_v3.onnx", synth_weights.s3tok_state(s3_cfg, seed=12), s3_cfg)
+    os.environ["FY_S3TOK_CONFIG"] = str(d / "s3.json")
+    try:
+        a = CosyVoiceFrontEndB200(str(d / "campplus.npz"), str(d / "s3tok.npz"))
+        b = CosyVoiceFrontEndB200(str(tmp_path / "campplus.onnx"), str(tmp_path / "speech_tokenizer_v3.onnx"))
+    finally:
+        del os.environ["FY_S3TOK_CONFIG"]
+    wav = str(d / "wav" / f"{keys[1]}.wav")
+    ea, eb = a._extract_spk_embedding(wav)[0].cpu(), b._extract_spk_embedding(wav)[0].cpu()
+    assert float(torch.nn.functional.cosine_similarity(ea, eb, dim=0)) >= 0.99999     # folding moves rounding only
+    ta, tb = a._extract_speech_token(wav)[0].cpu(), b._extract_speech_token(wav)[0].cpu()
+    assert torch.equal(ta, tb)                                                         # same weights bit for bit

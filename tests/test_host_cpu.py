@@ -192,7 +192,7 @@ def test_onnx_initializer_reader(tmp_path):
     st = weights.load_state(p)
     assert set(st) == {"conv.weight", "conv.bias"}
     assert np.array_equal(st["conv.weight"], a) and np.array_equal(st["conv.bias"], b)
-    with pytest.raises(KeyError, match="UNVERIFIED"):
+    with pytest.raises(KeyError, match="lacks 1 of 2"):
         weights.as_torch_state(st, ["conv.weight", "missing.tensor"])
     (tmp_path / "empty.onnx").write_bytes(_pb_field(1, 0, _pb_varint(8)))
     with pytest.raises(ValueError):
