@@ -35,6 +35,7 @@ PROTOTYPES = {
     "fy_version": (C.c_char_p, []),
     "fy_load_campplus": (_I, [_P, C.POINTER(FyTensor), _I, C.POINTER(FyCamConfig)]),
     "fy_load_s3tok": (_I, [_P, C.POINTER(FyTensor), _I, C.POINTER(FyS3Config)]),
+    "fy_resample_prepare": (_I, [_P, _I, _I]),
     "fy_resample": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I]),
     "fy_fbank_workspace_bytes": (_Z, [_I, _I]),
     "fy_fbank_cmn": (_I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _Z]),

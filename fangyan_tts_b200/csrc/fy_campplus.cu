@@ -19,6 +19,7 @@
 
 #include "fy_cam_kernels.cuh"
 #include "fy_common.cuh"
+#include "fy_plan.cuh"
 
 namespace fy {
 namespace {
@@ -52,7 +53,6 @@ struct CamPlan {
   BN out_bn;
   float* dense_w = nullptr; BN dense_bn;
   std::vector<void*> owned;
-  int* h_meta = nullptr; size_t h_meta_cap = 0; cudaEvent_t meta_ev = nullptr;
 };
 
 struct Loader {
@@ -173,8 +173,6 @@ void cam_free_plan(Ctx* c) {
   CamPlan* p = reinterpret_cast<CamPlan*>(c->cam_plan);
   if (!p) return;
   for (void* d : p->owned) cudaFree(d);
-  if (p->h_meta) cudaFreeHost(p->h_meta);
-  if (p->meta_ev) cudaEventDestroy(p->meta_ev);
   delete p;
   c->cam_plan = nullptr;
 }
@@ -277,7 +275,6 @@ int fy_load_campplus(fy_ctx* ctx, const fy_tensor* t, int n, const fy_campplus_c
     FY_TRY(dev_upload(p, std::vector<float>(w->h_data, w->h_data + (size_t)cfg->embed_dim * 2 * ch), &p->dense_w));
     FY_TRY(load_bn(L, "dense_bn", cfg->embed_dim, false, &p->dense_bn));
   }
-  FY_CUDA(cudaEventCreateWithFlags(&p->meta_ev, cudaEventDisableTiming));
   return FY_OK;
 }
 
@@ -350,45 +347,31 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   FY_CHECK((reinterpret_cast<uintptr_t>(ws) & 255) == 0, FY_ERR_ARG, "fy_campplus_forward: workspace must be 256-byte aligned");
   const fy_campplus_config& cf = p->cfg;
   cudaStream_t st = c->stream;
-  (void)frame_off;
 
   // ---- plan
-  std::vector<int> B(n_utts), T2(n_utts), SB(n_utts);
   int row = 0, nseg = 0;
   double vT = 0, vT2 = 0;  // valid frames at 100 / 50 Hz, for algorithmic FLOP accounting
   for (int u = 0; u < n_utts; ++u) {
     const int T = h_frame_off[u + 1] - h_frame_off[u];
     FY_CHECK(T >= 3, FY_ERR_ARG, "fy_campplus_forward: utterance %d has %d frames (need >= 3)", u, T);
-    T2[u] = (T - 1) / 2 + 1;
-    const int ns = (T2[u] + cf.seg_len - 1) / cf.seg_len;
-    B[u] = row; SB[u] = nseg;
-    vT += T; vT2 += T2[u];
-    row += T2[u] + 2;
-    nseg += ns;
+    const int t2 = (T - 1) / 2 + 1;
+    vT += T; vT2 += t2;
+    row += t2 + 2;
+    nseg += (t2 + cf.seg_len - 1) / cf.seg_len;
   }
   Layout lay = make_layout(p, n_utts, row, nseg);
   FY_CHECK(lay.total <= ws_bytes, FY_ERR_NOMEM, "fy_campplus_forward: workspace %zu < %zu bytes", ws_bytes, lay.total);
   const int R50 = lay.R50, R100 = lay.R100;
-  if (p->h_meta_cap < lay.meta_ints) {
-    if (p->h_meta) { FY_CUDA(cudaEventSynchronize(p->meta_ev)); FY_CUDA(cudaFreeHost(p->h_meta)); }
-    p->h_meta_cap = lay.meta_ints * 2;
-    FY_CUDA(cudaMallocHost(&p->h_meta, p->h_meta_cap * 4));
-  } else {
-    FY_CUDA(cudaEventSynchronize(p->meta_ev));
-  }
-  int* hm = p->h_meta;
-  std::fill(hm, hm + lay.meta_ints, -1);
-  for (int u = 0; u < n_utts; ++u) {
-    hm[lay.m_B + u] = B[u]; hm[lay.m_T2 + u] = T2[u]; hm[lay.m_segbase + u] = SB[u];
-    const int T = h_frame_off[u + 1] - h_frame_off[u];
-    for (int t = 0; t < T; ++t) hm[lay.m_rowsrc + 2 * B[u] + 2 + t] = h_frame_off[u] + t;
-    for (int t = 0; t < T2[u]; ++t) hm[lay.m_rowseg + B[u] + t] = SB[u] + t / cf.seg_len;
-    for (int k = 0; k * cf.seg_len < T2[u]; ++k) hm[lay.m_segutt + SB[u] + k] = u;
-  }
+  // per-row metadata is built on the device from frame_off (fy_plan.cuh); the host only needed the totals above
   uint8_t* base = reinterpret_cast<uint8_t*>(ws);
   int* d_meta = reinterpret_cast<int*>(base + lay.o_meta);
-  FY_CUDA(cudaMemcpyAsync(d_meta, hm, lay.meta_ints * 4, cudaMemcpyHostToDevice, st));
-  FY_CUDA(cudaEventRecord(p->meta_ev, st));
+  plan::cam_scan_kernel<<<1, plan::kScanThreads, 0, st>>>(frame_off, n_utts, cf.seg_len, d_meta + lay.m_B, d_meta + lay.m_T2,
+                                                          d_meta + lay.m_segbase);
+  plan::cam_fill_kernel<<<std::min((R100 + 255) / 256, 4 * c->num_sms), 256, 0, st>>>(
+      frame_off, n_utts, cf.seg_len, d_meta + lay.m_B, d_meta + lay.m_T2, d_meta + lay.m_segbase, R100, R50, nseg,
+      d_meta + lay.m_rowsrc, d_meta + lay.m_rowseg, d_meta + lay.m_segutt);
+  FY_CUDA(cudaGetLastError());
+  c->launches += 2;
   const int *d_B = d_meta + lay.m_B, *d_T2 = d_meta + lay.m_T2, *d_segbase = d_meta + lay.m_segbase;
   const int *d_rowsrc = d_meta + lay.m_rowsrc, *d_rowseg = d_meta + lay.m_rowseg, *d_segutt = d_meta + lay.m_segutt;
   auto I = [&](size_t off) { return reinterpret_cast<int*>(base + off); };

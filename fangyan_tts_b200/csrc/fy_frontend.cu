@@ -660,47 +660,67 @@ int fy_matcha_mel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pc
   return FY_OK;
 }
 
+namespace {
+struct ResampleSpec { int orig, newf, width, K; double base; };
+ResampleSpec resample_spec(int orig_freq, int new_freq) {
+  int a = orig_freq, b = new_freq;
+  while (b) { int t = a % b; a = b; b = t; }
+  ResampleSpec r;
+  r.orig = orig_freq / a; r.newf = new_freq / a;
+  const double lpw = 6.0, rolloff = 0.99;
+  r.base = (double)(r.orig < r.newf ? r.orig : r.newf) * rolloff;
+  r.width = (int)ceil(lpw * r.orig / r.base);
+  r.K = 2 * r.width + r.orig;
+  return r;
+}
+}  // namespace
+
+// torchaudio _get_sinc_resample_kernel (functional.py:1305-1402): hann-windowed sinc, width 6, rolloff 0.99, built in
+// float64 and rounded to fp32 -- except the phase offset -p/new, which torchaudio computes as a float32 division (its
+// arange there is int64), a quirk reproduced below.  Built once per reduced (orig, new) pair and kept by the context:
+// this is the call that allocates and copies synchronously, so that fy_resample itself never does.
+int fy_resample_prepare(fy_ctx* ctx, int orig_freq, int new_freq) {
+  FY_CHECK(ctx && orig_freq > 0 && new_freq > 0 && orig_freq != new_freq, FY_ERR_ARG, "fy_resample_prepare: bad arguments (%d -> %d)",
+           orig_freq, new_freq);
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  const ResampleSpec r = resample_spec(orig_freq, new_freq);
+  auto key = std::make_pair(r.orig, r.newf);
+  if (c->resample_kern.count(key)) return FY_OK;
+  const double lpw = 6.0;
+  std::vector<float> h((size_t)r.newf * r.K);
+  for (int p = 0; p < r.newf; ++p)
+    for (int k = 0; k < r.K; ++k) {
+      const float phase = (float)(-p) / (float)r.newf;
+      double t = ((double)phase + (double)(k - r.width) / r.orig) * r.base;
+      if (t < -lpw) t = -lpw;
+      if (t > lpw) t = lpw;
+      const double cw = cos(t * M_PI / lpw / 2);
+      const double tp = t * M_PI;
+      const double sinc = tp == 0.0 ? 1.0 : sin(tp) / tp;
+      h[(size_t)p * r.K + k] = (float)(sinc * cw * cw * (r.base / r.orig));
+    }
+  float* dk = nullptr;
+  FY_CUDA(cudaSetDevice(c->device));
+  FY_TRY(upload(c, h, &dk));
+  c->resample_kern[key] = dk;
+  return FY_OK;
+}
+
 int fy_resample(fy_ctx* ctx, const float* in, const int32_t* in_off, float* out, const int32_t* out_off, int n_utts,
                 int total_out, int orig_freq, int new_freq) {
   FY_CHECK(ctx && in && in_off && out && out_off, FY_ERR_ARG, "fy_resample: NULL argument");
   FY_CHECK(n_utts > 0 && orig_freq > 0 && new_freq > 0 && orig_freq != new_freq, FY_ERR_ARG,
            "fy_resample: bad arguments (n_utts=%d, %d -> %d)", n_utts, orig_freq, new_freq);
   Ctx* c = reinterpret_cast<Ctx*>(ctx);
-  // torchaudio _get_sinc_resample_kernel (functional.py:1305-1402): hann-windowed sinc, width 6, rolloff 0.99,
-  // built in float64 and rounded to fp32 -- except the phase offset -p/new, which torchaudio computes as a float32
-  // division (its arange there is int64), a quirk reproduced below.  Cached per (orig, new).
-  int a = orig_freq, b = new_freq;
-  while (b) { int t = a % b; a = b; b = t; }
-  const int orig = orig_freq / a, newf = new_freq / a;
-  const double lpw = 6.0, rolloff = 0.99;
-  const double base = (double)(orig < newf ? orig : newf) * rolloff;
-  const int width = (int)ceil(lpw * orig / base);
-  const int K = 2 * width + orig;
-  std::map<std::pair<int, int>, float*>& cache = c->resample_kern;
-  float* dk = nullptr;
-  auto key = std::make_pair(orig, newf);
-  auto it = cache.find(key);
-  if (it == cache.end()) {
-    std::vector<float> h((size_t)newf * K);
-    for (int p = 0; p < newf; ++p)
-      for (int k = 0; k < K; ++k) {
-        const float phase = (float)(-p) / (float)newf;
-        double t = ((double)phase + (double)(k - width) / orig) * base;
-        if (t < -lpw) t = -lpw;
-        if (t > lpw) t = lpw;
-        const double cw = cos(t * M_PI / lpw / 2);
-        const double tp = t * M_PI;
-        const double sinc = tp == 0.0 ? 1.0 : sin(tp) / tp;
-        h[(size_t)p * K + k] = (float)(sinc * cw * cw * (base / orig));
-      }
-    FY_TRY(upload(c, h, &dk));
-    cache[key] = dk;
-  } else {
-    dk = it->second;
-  }
+  const ResampleSpec r = resample_spec(orig_freq, new_freq);
+  auto it = c->resample_kern.find(std::make_pair(r.orig, r.newf));
+  FY_CHECK(it != c->resample_kern.end(), FY_ERR_STATE,
+           "fy_resample: call fy_resample_prepare(ctx, %d, %d) once first (it builds the filter bank; launches never allocate)",
+           orig_freq, new_freq);
   if (total_out <= 0) return FY_OK;
-  resample_kernel<<<(total_out + 255) / 256, 256, 0, c->stream>>>(in, in_off, out, out_off, n_utts, total_out, dk, width,
-                                                                orig, newf);
+  resample_kernel<<<(total_out + 255) / 256, 256, 0, c->stream>>>(in, in_off, out, out_off, n_utts, total_out, it->second,
+                                                                r.width, r.orig, r.newf);
+  c->launches += 1;
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }

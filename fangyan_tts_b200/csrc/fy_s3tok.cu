@@ -14,6 +14,7 @@
 #include "fy_attention.cuh"
 #include "fy_attention_tc.cuh"
 #include "fy_common.cuh"
+#include "fy_plan.cuh"
 #include "fy_s3_kernels.cuh"
 
 namespace fy {
@@ -38,10 +39,7 @@ struct S3Plan {
   float *rope_cos = nullptr, *rope_sin = nullptr;
   int rope_len = 0;
   std::vector<void*> owned;
-  // pinned staging for per-call metadata
-  int* h_meta = nullptr;
-  size_t h_meta_cap = 0;
-  cudaEvent_t meta_ev = nullptr;
+  bool attn_configured = false;   // cudaFuncSetAttribute done for this context's device
 };
 
 const fy_tensor* find(const fy_tensor* t, int n, const std::string& name) {
@@ -121,7 +119,7 @@ struct Layout {  // per-call sizes derived from the frame counts
   int n_utts = 0, Rtok = 0, R1 = 0, Rmel = 0, n_attn_tiles = 0, Tmax = 0;
   size_t o_meta, o_mel, o_c1, o_x, o_xn, o_q, o_k, o_v, o_att, o_h, total;
   // meta sub-offsets (ints)
-  size_t m_P, m_L, m_row1, m_rutt, m_rpos, m_tiles, m_tiles128, meta_ints;
+  size_t m_P, m_L, m_t64, m_t128, m_row1, m_rutt, m_rpos, m_tiles, m_tiles128, meta_ints;
 };
 
 int token_len(int T) { const int l1 = (T - 1) / 2 + 1; return (l1 - 1) / 2 + 1; }
@@ -137,7 +135,9 @@ Layout make_layout(const fy_s3_config& c, int W, int n_utts, int rtok, int n_til
   const size_t D = c.d_model;
   l.m_P = 0;
   l.m_L = l.m_P + n_utts;
-  l.m_row1 = l.m_L + n_utts;
+  l.m_t64 = l.m_L + n_utts;
+  l.m_t128 = l.m_t64 + n_utts;
+  l.m_row1 = l.m_t128 + n_utts;
   l.m_rutt = l.m_row1 + l.R1;
   l.m_rpos = l.m_rutt + rtok;
   l.m_tiles = l.m_rpos + rtok;
@@ -165,8 +165,6 @@ void s3_free_plan(Ctx* c) {
   S3Plan* p = reinterpret_cast<S3Plan*>(c->s3_plan);
   if (!p) return;
   for (void* d : p->owned) cudaFree(d);
-  if (p->h_meta) cudaFreeHost(p->h_meta);
-  if (p->meta_ev) cudaEventDestroy(p->meta_ev);
   delete p;
   c->s3_plan = nullptr;
 }
@@ -281,7 +279,9 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
       FY_TRY(dev_upload(p, hs, &p->rope_sin));
     }
   }
-  FY_CUDA(cudaEventCreateWithFlags(&p->meta_ev, cudaEventDisableTiming));
+  FY_CUDA(cudaFuncSetAttribute(attn_tc::attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               attn_tc::kSmemBytes));
+  p->attn_configured = true;
   FY_CUDA(cudaFuncSetAttribute(attn::attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                attn::smem_bytes<true>()));
   FY_CUDA(cudaFuncSetAttribute(attn::attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -314,13 +314,12 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   cudaStream_t st = c->stream;
 
   // ---- plan the packed layout on the host
-  std::vector<int> P(n_utts), L(n_utts);
+  std::vector<int> L(n_utts);
   int row = 0, tiles = 0, Tmax = 0;
   double vtok = 0, vc1 = 0, attn_flops = 0;  // valid rows, for algorithmic FLOP accounting
   for (int u = 0; u < n_utts; ++u) {
     const int T = h_frame_off[u + 1] - h_frame_off[u];
     FY_CHECK(T > 0, FY_ERR_ARG, "fy_s3tok_encode_fsq: utterance %d has %d mel frames", u, T);
-    P[u] = row;
     L[u] = token_len(T);
     FY_CHECK(L[u] <= p->rope_len, FY_ERR_ARG, "utterance %d has %d tokens, rope table holds %d", u, L[u], p->rope_len);
     row += L[u] + 1;
@@ -332,47 +331,22 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   }
   Layout lay = make_layout(cf, W, n_utts, row, tiles);
   FY_CHECK(lay.total <= ws_bytes, FY_ERR_NOMEM, "fy_s3tok_encode_fsq: workspace %zu < %zu bytes", ws_bytes, lay.total);
-  // ---- metadata: host staging (pinned, guarded by an event) -> device
-  if (p->h_meta_cap < lay.meta_ints) {
-    if (p->h_meta) { FY_CUDA(cudaEventSynchronize(p->meta_ev)); FY_CUDA(cudaFreeHost(p->h_meta)); }
-    p->h_meta_cap = lay.meta_ints * 2;
-    FY_CUDA(cudaMallocHost(&p->h_meta, p->h_meta_cap * 4));
-  } else {
-    FY_CUDA(cudaEventSynchronize(p->meta_ev));
-  }
-  int* hm = p->h_meta;
-  std::fill(hm, hm + lay.meta_ints, -1);
-  for (int u = 0; u < n_utts; ++u) {
-    hm[lay.m_P + u] = P[u];
-    hm[lay.m_L + u] = L[u];
-    const int T = h_frame_off[u + 1] - h_frame_off[u];
-    const int L1 = (T - 1) / 2 + 1;
-    for (int t = 0; t < L1; ++t) hm[lay.m_row1 + 2 * P[u] + 1 + t] = u;
-    for (int t = 0; t < L[u]; ++t) {
-      hm[lay.m_rutt + P[u] + t] = u;
-      hm[lay.m_rpos + P[u] + t] = t;
-    }
-  }
-  {
-    int ti = 0;
-    for (int u = 0; u < n_utts; ++u)
-      for (int q0 = 0; q0 < L[u]; q0 += 64) {
-        hm[lay.m_tiles + 2 * ti] = u;
-        hm[lay.m_tiles + 2 * ti + 1] = q0;
-        ++ti;
-      }
-  }
+  // ---- metadata: built on the device from frame_off (fy_plan.cuh); the host only needed the totals above
   int tiles128 = 0;
-  for (int u = 0; u < n_utts; ++u)
-    for (int q0 = 0; q0 < L[u]; q0 += 128) {
-      hm[lay.m_tiles128 + 2 * tiles128] = u;
-      hm[lay.m_tiles128 + 2 * tiles128 + 1] = q0;
-      ++tiles128;
-    }
+  for (int u = 0; u < n_utts; ++u) tiles128 += (L[u] + 127) / 128;
   uint8_t* base = reinterpret_cast<uint8_t*>(ws);
   int* d_meta = reinterpret_cast<int*>(base + lay.o_meta);
-  FY_CUDA(cudaMemcpyAsync(d_meta, hm, lay.meta_ints * 4, cudaMemcpyHostToDevice, st));
-  FY_CUDA(cudaEventRecord(p->meta_ev, st));
+  plan::s3_scan_kernel<<<1, plan::kScanThreads, 0, st>>>(frame_off, n_utts, d_meta + lay.m_P, d_meta + lay.m_L,
+                                                         d_meta + lay.m_t64, d_meta + lay.m_t128);
+  {
+    const int top = std::max(std::max(lay.Rtok, lay.R1), tiles);
+    plan::s3_fill_kernel<<<std::min((top + 255) / 256, 4 * c->num_sms), 256, 0, st>>>(
+        frame_off, n_utts, d_meta + lay.m_P, d_meta + lay.m_L, d_meta + lay.m_t64, d_meta + lay.m_t128, lay.Rtok, lay.R1,
+        tiles, tiles128, d_meta + lay.m_row1, d_meta + lay.m_rutt, d_meta + lay.m_rpos,
+        reinterpret_cast<int2*>(d_meta + lay.m_tiles), reinterpret_cast<int2*>(d_meta + lay.m_tiles128));
+  }
+  FY_CUDA(cudaGetLastError());
+  c->launches += 2;
   const int* d_P = d_meta + lay.m_P;
   const int* d_L = d_meta + lay.m_L;
   const int* d_row1 = d_meta + lay.m_row1;
@@ -437,12 +411,6 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   const bool attn_tc_on = attn_tc_env && W == 2 && cf.d_model / cf.n_head == 64 && cf.n_head % attn_tc::kHeadsPerCta == 0;
   attn_tc::Params tc_params;
   if (attn_tc_on) {
-    static bool configured = false;
-    if (!configured) {
-      FY_CUDA(cudaFuncSetAttribute(attn_tc::attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   attn_tc::kSmemBytes));
-      configured = true;
-    }
     FY_TRY(make_tmap_bf16(&tc_params.tm_kv, b_k, Rtok, D * W, D * W, 64));
     FY_TRY(make_tmap_bf16(&tc_params.tm_v, b_v, Rtok, D * W, D * W, 64));
     tc_params.q = b_q; tc_params.out = b_att; tc_params.ld = D * W; tc_params.lo_off = D; tc_params.rows = Rtok;

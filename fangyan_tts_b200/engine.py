@@ -153,6 +153,7 @@ class Engine:
         in_off, out_off = _offsets(lengths), _offsets(out_len)
         out = torch.empty(int(out_off[-1]), dtype=torch.float32, device=self.device)
         d_in, d_out = self._dev_i32(in_off), self._dev_i32(out_off)
+        check(self.lib.fy_resample_prepare(self.h, orig_freq, new_freq))     # builds the filter bank on first use
         check(self.lib.fy_resample(self.h, _ptr(wave), _ptr(d_in), _ptr(out), _ptr(d_out), len(lengths),
                                    int(out_off[-1]), orig_freq, new_freq))
         return out, out_len

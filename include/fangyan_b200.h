@@ -10,7 +10,13 @@
  *   - utterances are passed PACKED: one contiguous array plus an int32 offsets array of n_utts + 1 entries
  *     (exclusive prefix sums), never padded.  The reference runs every utterance alone at its true length
  *     (tools/extract_embedding.py:25-42), so there is no padding to reproduce.
- *   - launches are asynchronous on the context's stream (fy_set_stream); nothing here synchronises.
+ *   - launch calls (fy_resample, fy_fbank_cmn, fy_logmel, fy_matcha_mel, fy_campplus_forward, fy_s3tok_encode_fsq,
+ *     fy_speaker_*) are asynchronous on the context's stream (fy_set_stream): they neither synchronise nor allocate
+ *     nor copy from host memory -- per-call row maps are derived on the device from the offsets arrays -- so a
+ *     sequence of them can be captured in a CUDA graph.  h_frame_off arguments are read on the host during the call
+ *     (totals for grid sizes and the workspace check) and may be freed as soon as it returns.
+ *     The calls that DO allocate and synchronise are the set-up ones: fy_create, fy_load_*, fy_resample_prepare,
+ *     fy_profile_read, fy_destroy.
  *   - the caller owns inputs, outputs and the workspace; the library owns weights and lookup tables.
  *   - a fy_ctx is not thread-safe: one per worker / GPU.
  */
@@ -80,7 +86,9 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* h_tensors, int n, const fy_s3_co
  * tools/extract_embedding.py:27-28, tools/extract_speech_token.py:29-30, cosyvoice/utils/file_utils.py:47-49.
  * One launch resamples a packed batch that shares one input rate.  Output length per utterance is
  * ceil(new * n_in / orig) (after dividing both rates by their gcd); out_off must hold those prefix sums and
- * total_out is their last entry (host value). */
+ * total_out is their last entry (host value).  fy_resample_prepare builds the windowed-sinc filter bank of a rate
+ * pair (torchaudio rebuilds it inside every Resample(...) construction) and must have been called once for it. */
+int fy_resample_prepare(fy_ctx* ctx, int orig_freq, int new_freq);
 int fy_resample(fy_ctx* ctx, const float* in, const int32_t* in_off, float* out, const int32_t* out_off, int n_utts,
                 int total_out, int orig_freq, int new_freq);
 
