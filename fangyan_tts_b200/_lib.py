@@ -25,6 +25,11 @@ class FyCamConfig(C.Structure):
                 ("seg_len", C.c_int32), ("bn_eps", C.c_float)]
 
 
+class FyWavInfo(C.Structure):
+    _fields_ = [("frames", C.c_int64), ("data_offset", C.c_int64), ("channels", C.c_int32), ("sample_rate", C.c_int32),
+                ("format", C.c_int32), ("bits", C.c_int32), ("status", C.c_int32), ("reserved", C.c_int32)]
+
+
 _P, _I, _Z = C.c_void_p, C.c_int, C.c_size_t
 # name -> (restype, argtypes); mirrors include/fangyan_b200.h one to one
 PROTOTYPES = {
@@ -35,6 +40,9 @@ PROTOTYPES = {
     "fy_version": (C.c_char_p, []),
     "fy_load_campplus": (_I, [_P, C.POINTER(FyTensor), _I, C.POINTER(FyCamConfig)]),
     "fy_load_s3tok": (_I, [_P, C.POINTER(FyTensor), _I, C.POINTER(FyS3Config)]),
+    "fy_wav_scan": (_I, [C.POINTER(C.c_char_p), _I, C.POINTER(FyWavInfo), _I]),
+    "fy_wav_read_s16": (_I, [C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(_P), _I, _I,
+                            C.POINTER(C.c_int32)]),
     "fy_resample_prepare": (_I, [_P, _I, _I]),
     "fy_resample": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I]),
     "fy_fbank_workspace_bytes": (_Z, [_I, _I]),

@@ -62,3 +62,59 @@ def read_wav(path: str, key: str = "?"):
     if tag == 3 and bits == 32:
         return np.frombuffer(raw, dtype="<f4").reshape(n, ch).copy(), sr
     raise AudioDecodeError(f"utterance {key}: {path}: unsupported WAV encoding (format tag {tag}, {bits} bits)")
+
+
+# ---------------------------------------------------------------------------------------------- native fast path (N2)
+def scan_wavs(keys, paths, n_threads: int = 8):
+    """Header pass over every file with the library's thread pool (fy_wav_scan): returns a dict of numpy arrays
+    frames / channels / sample_rate / data_offset / simple (plain PCM16, readable straight into pinned memory by
+    read_s16_into).  Files with long headers are re-parsed by read_wav; unreadable or non-WAV files raise
+    AudioDecodeError naming the utterance key, as the per-file reader does."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    n = len(paths)
+    arr = (C.c_char_p * n)(*[p.encode() for p in paths])
+    info = (_lib.FyWavInfo * n)()
+    _lib.check(lib.fy_wav_scan(arr, n, info, max(1, n_threads)))
+    a = np.frombuffer(info, dtype=np.dtype([("frames", "<i8"), ("data_offset", "<i8"), ("channels", "<i4"),
+                                            ("sample_rate", "<i4"), ("format", "<i4"), ("bits", "<i4"),
+                                            ("status", "<i4"), ("reserved", "<i4")]), count=n).copy()
+    for i in np.nonzero(a["status"] != 0)[0].tolist():
+        if a["status"][i] == -3:                     # long header: full parse in Python
+            x, sr = read_wav(paths[i], keys[i])
+            a["frames"][i], a["channels"][i], a["sample_rate"][i], a["format"][i], a["bits"][i] = x.shape[0], x.shape[1], sr, 0, 0
+            continue
+        if a["status"][i] == -1:
+            raise AudioDecodeError(f"utterance {keys[i]}: cannot read {paths[i]}")
+        raise AudioDecodeError(f"utterance {keys[i]}: {paths[i]} is not a RIFF/WAVE file (mp3/flac input is not supported; "
+                               "convert with prepare_training_data.py first)")
+    simple = (a["status"] == 0) & (a["format"] == 1) & (a["bits"] == 16)
+    return {"frames": a["frames"], "channels": a["channels"], "sample_rate": a["sample_rate"],
+            "data_offset": a["data_offset"], "simple": simple, "_paths": arr}
+
+
+def read_s16_into(scan, indices, dst: np.ndarray, n_threads: int = 8, keys=None):
+    """Samples of the `simple` mono files `indices` -> consecutive slices of the int16 array `dst` (e.g. a view of a
+    pinned staging buffer), read by the library's threads with the GIL released."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    n = len(indices)
+    idx = np.asarray(indices, dtype=np.int64)
+    cnt = np.ascontiguousarray(scan["frames"][idx] * scan["channels"][idx], dtype=np.int64)
+    off = np.ascontiguousarray(scan["data_offset"][idx], dtype=np.int64)
+    starts = np.zeros(n, dtype=np.int64)
+    np.cumsum(cnt[:-1], out=starts[1:])
+    if int(starts[-1] + cnt[-1] if n else 0) > dst.size:
+        raise ValueError("destination too small")
+    base = dst.ctypes.data
+    ptrs = (C.c_void_p * n)(*[base + 2 * int(s) for s in starts])
+    paths = (C.c_char_p * n)(*[scan["_paths"][int(i)] for i in idx])
+    bad = C.c_int32(-1)
+    rc = lib.fy_wav_read_s16(paths, off.ctypes.data_as(C.POINTER(C.c_int64)), cnt.ctypes.data_as(C.POINTER(C.c_int64)),
+                             ptrs, n, max(1, n_threads), C.byref(bad))
+    if rc != 0:
+        k = keys[int(idx[bad.value])] if keys is not None and bad.value >= 0 else "?"
+        raise AudioDecodeError(f"utterance {k}: {lib.fy_last_error().decode()}")
+    return cnt

@@ -96,7 +96,7 @@ def _n_gpus() -> int:
 def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: bool):
     import torch
     from . import distributed as D
-    from .audio_io import read_wav
+    from .audio_io import read_s16_into, read_wav, scan_wavs
     from .configs import campplus_config, s3_config
     from .engine import Engine, kaldi_num_frames
     from .pipeline import Extractor, Utt, plan_batches, shard_indices, split_tokens
@@ -110,6 +110,12 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         torch.cuda.set_device(local_rank)
         D.init(rank, world, "nccl", port, torch.device("cuda", local_rank))
     t_start = time.perf_counter()
+    utt2wav = kaldi_io.read_table(os.path.join(args.dir, "wav.scp"))
+    keys, paths = list(utt2wav.keys()), list(utt2wav.values())
+    pool = ThreadPoolExecutor(max_workers=max(1, args.num_thread))
+    n_io = max(1, args.num_thread)
+    # header pass over every file (native threads, GIL released) runs under the engine set-up and the weight upload
+    scan_job = pool.submit(lambda: (time.perf_counter(), scan_wavs(keys, paths, n_io), time.perf_counter()))
     eng = Engine(local_rank, os.environ.get("FY_PRECISION", "bf16x3"))
     cfg = campplus_config() if stage == 1 else s3_config()
     # .onnx files are mapped by graph topology (weights.py); .npz / .pt carry our tensor names
@@ -122,15 +128,16 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
     del state
 
     t_weights = time.perf_counter() - t_start
-    utt2wav = kaldi_io.read_table(os.path.join(args.dir, "wav.scp"))
-    keys, paths = list(utt2wav.keys()), list(utt2wav.values())
-    pool = ThreadPoolExecutor(max_workers=max(1, args.num_thread))
     t0 = time.perf_counter()
-    heads = scan_durations(keys, paths, pool)
-    n16 = [len16k(fr, sr) for fr, _, sr in heads]
+    s0, scan, s1 = scan_job.result()
+    t_scan_wait, t_scan = time.perf_counter() - t0, s1 - s0
+    n16 = [len16k(int(fr), int(sr)) for fr, sr in zip(scan["frames"], scan["sample_rate"])]
     dur = [n / SR for n in n16]
     mine = shard_indices(dur, rank, world)
-    t_scan = time.perf_counter() - t0
+    # plain 16 kHz mono PCM16 (what prepare_training_data.py writes): read by the library straight into the pinned ring
+    direct = scan["simple"] & (scan["sample_rate"] == SR) & (scan["channels"] == 1)
+    if os.environ.get("FY_NATIVE_READER", "1") == "0":
+        direct = direct & False
     ex = Extractor(eng, float(os.environ.get("FY_BATCH_SECONDS", "2400")), int(os.environ.get("FY_BATCH_UTTS", "4096")))
     dev = eng.device
     tm = {"decode_wait_s": 0.0, "gpu_events": []}
@@ -139,18 +146,38 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         x, sr = read_wav(paths[i], keys[i])
         return Utt(x, sr)
 
+    def start(b):
+        """Begin loading one batch: the native reader fills a slot of the upload ring in a pool thread (one call per
+        batch, GIL released), anything else is decoded per file by the Python reader."""
+        if all(direct[i] for i in b):
+            lens = [n16[i] for i in b]
+            total = int(sum(lens))
+            slot, view = ex.ring.acquire(total)
+            return b, (slot, total, lens, pool.submit(read_s16_into, scan, b, view, n_io, keys))
+        return b, [pool.submit(load_one, i) for i in b]
+
     def batches_of(todo):
-        """(indices, decoded utterances) per batch; the time this rank's main thread spends blocked on the reader pool
-        is accumulated in tm (the GPU keeps running the previous batch meanwhile: nothing in the loop synchronises)."""
+        """(indices, device PCM, lengths) or (indices, decoded utterances, None) per batch, two batches ahead; the time
+        this rank's main thread spends blocked on the readers is accumulated in tm (the GPU keeps running the previous
+        batch meanwhile: nothing in the loop synchronises)."""
         local_dur = [dur[i] for i in todo]
         plan = [[todo[j] for j in b] for b in plan_batches(local_dur, ex.max_batch_seconds, ex.max_batch_utts)]
-        it = iter(_progress(prefetch(plan, load_one, pool), len(plan), rank, f"stage {stage}"))
-        while True:
+        bar = _progress(range(len(plan)), len(plan), rank, f"stage {stage}")
+        it = iter(plan)
+        pending = collections.deque(start(b) for b in itertools.islice(it, 2))
+        for _ in bar:
+            b, job = pending.popleft()
             t = time.perf_counter()
-            item = next(it, None)
+            if isinstance(job, tuple):
+                slot, total, lens, fut = job
+                fut.result()                           # a read error propagates here with the utterance key
+                item = (b, ex.ring.submit(slot, total), lens)
+            else:
+                item = (b, [f.result() for f in job], None)
             tm["decode_wait_s"] += time.perf_counter() - t
-            if item is None:
-                return
+            nxt = next(it, None)
+            if nxt is not None:
+                pending.append(start(nxt))
             a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             yield item
@@ -175,8 +202,8 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         ssum = torch.zeros(len(spk_names), 192, device=dev)
         scnt = torch.zeros(len(spk_names), dtype=torch.int32, device=dev)
         order, emb_parts = [], []
-        for b, utts in batches_of(mine):
-            emb = ex.embed_batch(utts)
+        for b, x, lens in batches_of(mine):
+            emb = ex.embed_batch(x) if lens is None else ex.embed_pcm(x, lens)
             eng.speaker_sum(emb, to_dev(spk_of[b], np.int32), len(spk_names), ssum, scnt)
             order.extend(b)
             emb_parts.append(emb)
@@ -205,8 +232,8 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
             logging.warning("do not support extract speech token for audio longer than 30s (%s)", keys[i])
         todo = [i for i in mine if not n16[i] / SR > 30 and n16[i] >= 160]
         order, cnt_all, tok_parts = [], [], []
-        for b, utts in batches_of(todo):
-            tok, counts = ex.tokenize_batch(utts)
+        for b, x, lens in batches_of(todo):
+            tok, counts = ex.tokenize_batch(x) if lens is None else ex.tokenize_pcm(x, lens)
             order.extend(b)
             cnt_all.extend(counts)
             tok_parts.append(tok)
@@ -232,7 +259,9 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
             "stage": stage, "utts": len(keys), "audio_hours": sum(dur) / 3600.0, "gpus": world, "wall_s": wall,
             "precision": eng.precision, "audio_hours_per_s": sum(dur) / 3600.0 / wall,
             # rank 0's view; decode+stage and GPU overlap inside loop_s (reader pool + upload ring run ahead of the kernels)
-            "split_s": {"engine_and_weights": t_weights, "header_scan": t_scan, "loop": t_loop,
+            "native_reader_utts": int(direct.sum()),
+            "split_s": {"engine_and_weights": t_weights, "header_scan": t_scan, "header_scan_exposed": t_scan_wait,
+                        "loop": t_loop,
                         "loop_decode_wait": tm["decode_wait_s"], "loop_pack_upload": ex.ring.pack_seconds,
                         "loop_gpu_busy": gpu_s, "gather": t_gather, "tolist_save": t_save}}) + "\n")
     pool.shutdown()

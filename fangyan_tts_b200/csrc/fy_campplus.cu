@@ -349,7 +349,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   cudaStream_t st = c->stream;
 
   // ---- plan
-  int row = 0, nseg = 0;
+  int row = 0, nseg = 0, max_seg = 0;
   double vT = 0, vT2 = 0;  // valid frames at 100 / 50 Hz, for algorithmic FLOP accounting
   for (int u = 0; u < n_utts; ++u) {
     const int T = h_frame_off[u + 1] - h_frame_off[u];
@@ -358,7 +358,10 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
     vT += T; vT2 += t2;
     row += t2 + 2;
     nseg += (t2 + cf.seg_len - 1) / cf.seg_len;
+    max_seg = std::max(max_seg, (t2 + cf.seg_len - 1) / cf.seg_len);
   }
+  static const bool gate_env = [] { const char* e = getenv("FY_CAM_FUSED_GATE"); return !(e && e[0] == '0'); }();
+  const bool fused_gate = gate_env && max_seg <= camk::kGateMaxSeg;
   Layout lay = make_layout(p, n_utts, row, nseg);
   FY_CHECK(lay.total <= ws_bytes, FY_ERR_NOMEM, "fy_campplus_forward: workspace %zu < %zu bytes", ws_bytes, lay.total);
   const int R50 = lay.R50, R100 = lay.R100;
@@ -460,9 +463,14 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
         g.epi.scale = d.bn2.scale; g.epi.bias = d.bn2.shift; g.epi.row_idx = d_rowseg;
         FY_TRY(run_gemm(c, g, 2.0 * vT2 * 128 * d.cin));
       }
-      c->launches += 3;  // bnrelu, cam_segsum, cam_gate
-      camk::cam_segsum_kernel<<<nseg, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, d_segutt, cf.seg_len, segsum);
-      camk::cam_gate_kernel<<<nseg, 128, 0, st>>>(segsum, d_T2, d_segbase, d_segutt, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
+      if (fused_gate) {
+        c->launches += 2;  // bnrelu, cam_ctx_gate
+        camk::cam_ctx_gate_kernel<<<n_utts, 256, 0, st>>>(hb, d_B, d_T2, d_segbase, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
+      } else {
+        c->launches += 3;  // bnrelu, cam_segsum, cam_gate
+        camk::cam_segsum_kernel<<<nseg, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, d_segutt, cf.seg_len, segsum);
+        camk::cam_gate_kernel<<<nseg, 128, 0, st>>>(segsum, d_T2, d_segbase, d_segutt, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
+      }
       {
         GemmArgs g;
         g.tmap_a = m_hb; g.tmap_b = d.ml; g.M = R50; g.N = 32; g.op = OP_F16;

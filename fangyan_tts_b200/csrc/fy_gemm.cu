@@ -667,10 +667,13 @@ EncodeTiledFn get_encode() {
 template <int BN, int OP, int NCTA>
 int launch_bn(const GemmArgs& a, int num_sms, cudaStream_t st) {
   using C = Cfg<BN, NCTA>;
-  static bool configured = false;
-  if (!configured) {
+  // function attributes belong to a device's context: configured once per device, not once per process
+  static bool configured[64] = {false};
+  int dev = 0;
+  FY_CUDA(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
     FY_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, OP, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    configured = true;
+    configured[dev & 63] = true;
   }
   const int tiles = ((a.M + BM * NCTA - 1) / (BM * NCTA)) * (a.N / BN);
   const int slots = num_sms * C::kCtasPerSm / NCTA;

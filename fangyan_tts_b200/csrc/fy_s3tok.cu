@@ -10,8 +10,10 @@
 #include <string.h>
 
 #include <algorithm>
+#include <initializer_list>
 
 #include "fy_attention.cuh"
+#include "fy_attention_pp.cuh"
 #include "fy_attention_tc.cuh"
 #include "fy_common.cuh"
 #include "fy_plan.cuh"
@@ -40,6 +42,8 @@ struct S3Plan {
   int rope_len = 0;
   std::vector<void*> owned;
   bool attn_configured = false;   // cudaFuncSetAttribute done for this context's device
+  float* stage = nullptr;         // fp32 staging of one weight matrix during fy_load_s3tok
+  size_t stage_cap = 0;
 };
 
 const fy_tensor* find(const fy_tensor* t, int n, const std::string& name) {
@@ -54,6 +58,18 @@ int64_t numel(const fy_tensor* t) {
   return n;
 }
 
+// Full-shape check (an element count alone lets a transposed square matrix through).
+bool shape_is(const fy_tensor* t, std::initializer_list<int64_t> want) {
+  if (t->ndim != (int)want.size()) return false;
+  int i = 0;
+  for (int64_t w : want)
+    if (t->shape[i++] != w) return false;
+  return true;
+}
+#define FY_SHAPE(t, ...)                                                                                           \
+  FY_CHECK(shape_is(t, {__VA_ARGS__}), FY_ERR_ARG, "fy_load_s3tok: tensor '%s' has the wrong shape (rank %d, first dims %lld x %lld)", \
+           (t)->name, (t)->ndim, (long long)(t)->shape[0], (long long)((t)->ndim > 1 ? (t)->shape[1] : 1))
+
 template <typename T>
 int dev_upload(S3Plan* p, const std::vector<T>& h, T** d) {
   FY_CUDA(cudaMalloc(d, h.size() * sizeof(T)));
@@ -62,17 +78,34 @@ int dev_upload(S3Plan* p, const std::vector<T>& h, T** d) {
   return FY_OK;
 }
 
-// fp32 [N, K] -> bf16 [N, K*W]: hi at [0, K), lo = bf16(x - hi) at [K, 2K) when W == 2.
+// fp32 [N, K] -> bf16 [N, K*W]: hi at [0, K), lo = bf16(x - hi) at [K, 2K) when W == 2.  The split runs on the device
+// (one streaming kernel per matrix over a staged fp32 copy): a 12-layer encoder has 236 M weights, which the host
+// loop this replaces took seconds to convert.
+__global__ void split_weight_kernel(const float* __restrict__ w, long long n, int K, int W, __nv_bfloat16* __restrict__ out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / K;
+    const int k = (int)(i - r * K);
+    const float x = w[i];
+    const __nv_bfloat16 hi = __float2bfloat16_rn(x);
+    out[r * K * W + k] = hi;
+    if (W == 2) out[r * K * 2 + K + k] = __float2bfloat16_rn(x - __bfloat162float(hi));
+  }
+}
+
 int upload_weight(S3Plan* p, const float* w, int64_t N, int64_t K, __nv_bfloat16** d) {
-  std::vector<__nv_bfloat16> h((size_t)N * K * p->W);
-  for (int64_t n = 0; n < N; ++n)
-    for (int64_t k = 0; k < K; ++k) {
-      const float x = w[n * K + k];
-      const __nv_bfloat16 hi = __float2bfloat16_rn(x);
-      h[(size_t)n * K * p->W + k] = hi;
-      if (p->W == 2) h[(size_t)n * K * 2 + K + k] = __float2bfloat16_rn(x - __bfloat162float(hi));
-    }
-  return dev_upload(p, h, d);
+  const size_t n = (size_t)N * K;
+  if (p->stage_cap < n) {
+    if (p->stage) cudaFree(p->stage);
+    p->stage = nullptr;
+    FY_CUDA(cudaMalloc(&p->stage, n * sizeof(float)));
+    p->stage_cap = n;
+  }
+  FY_CUDA(cudaMalloc(d, n * p->W * sizeof(__nv_bfloat16)));
+  p->owned.push_back(*d);
+  FY_CUDA(cudaMemcpy(p->stage, w, n * sizeof(float), cudaMemcpyHostToDevice));
+  split_weight_kernel<<<1184, 256>>>(p->stage, (long long)n, (int)K, p->W, *d);
+  FY_CUDA(cudaGetLastError());
+  return FY_OK;
 }
 
 #define NEED(var, name)                                                           \
@@ -165,6 +198,7 @@ void s3_free_plan(Ctx* c) {
   S3Plan* p = reinterpret_cast<S3Plan*>(c->s3_plan);
   if (!p) return;
   for (void* d : p->owned) cudaFree(d);
+  if (p->stage) cudaFree(p->stage);
   delete p;
   c->s3_plan = nullptr;
 }
@@ -194,7 +228,7 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
   const int64_t D = cfg->d_model, F = cfg->d_ff, NM = cfg->n_mels, KS = cfg->fsmn_kernel;
   {
     NEED(w, "conv1.weight"); NEED(b, "conv1.bias");
-    FY_CHECK(numel(w) == D * NM * 3, FY_ERR_ARG, "conv1.weight has wrong size");
+    FY_SHAPE(w, D, NM, 3);
     auto r = conv_tap_major(w->h_data, D, NM, 3);
     FY_TRY(upload_weight(p, r.data(), D, 3 * NM, &p->wc1));
     FY_TRY(upload_f32(p, b, D, &p->bc1));
@@ -202,7 +236,7 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
   }
   {
     NEED(w, "conv2.weight"); NEED(b, "conv2.bias");
-    FY_CHECK(numel(w) == D * D * 3, FY_ERR_ARG, "conv2.weight has wrong size");
+    FY_SHAPE(w, D, D, 3);
     auto r = conv_tap_major(w->h_data, D, D, 3);
     FY_TRY(upload_weight(p, r.data(), D, 3 * D, &p->wc2));
     FY_TRY(upload_f32(p, b, D, &p->bc2));
@@ -223,8 +257,7 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
     NEED(w2, pre + "fc2.weight"); NEED(b2, pre + "fc2.bias");
     FY_TRY(upload_f32(p, g1, D, &L.ln1_g)); FY_TRY(upload_f32(p, be1, D, &L.ln1_b));
     FY_TRY(upload_f32(p, g2, D, &L.ln2_g)); FY_TRY(upload_f32(p, be2, D, &L.ln2_b));
-    FY_CHECK(numel(wq) == D * D && numel(wk) == D * D && numel(wv) == D * D && numel(wo) == D * D, FY_ERR_ARG,
-             "layer %d attention weights have wrong size", i);
+    FY_SHAPE(wq, D, D); FY_SHAPE(wk, D, D); FY_SHAPE(wv, D, D); FY_SHAPE(wo, D, D);
     std::vector<float> qkv((size_t)3 * D * D), bqkv((size_t)3 * D, 0.f);
     memcpy(qkv.data(), wq->h_data, D * D * 4);
     memcpy(qkv.data() + D * D, wk->h_data, D * D * 4);
@@ -235,12 +268,12 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
     FY_TRY(dev_upload(p, bqkv, &L.bqkv));
     FY_TRY(upload_weight(p, wo->h_data, D, D, &L.wo));
     FY_TRY(upload_f32(p, bo, D, &L.bo));
-    FY_CHECK(numel(w1) == F * D && numel(w2) == D * F, FY_ERR_ARG, "layer %d MLP weights have wrong size", i);
+    FY_SHAPE(w1, F, D); FY_SHAPE(w2, D, F);
     FY_TRY(upload_weight(p, w1->h_data, F, D, &L.w1));
     FY_TRY(upload_f32(p, b1, F, &L.b1));
     FY_TRY(upload_weight(p, w2->h_data, D, F, &L.w2));
     FY_TRY(upload_f32(p, b2, D, &L.b2));
-    FY_CHECK(numel(fs) == D * KS, FY_ERR_ARG, "layer %d fsmn weight has wrong size", i);
+    FY_SHAPE(fs, D, 1, KS);
     std::vector<float> ft((size_t)KS * D);
     for (int64_t ch = 0; ch < D; ++ch)
       for (int64_t j = 0; j < KS; ++j) ft[j * D + ch] = fs->h_data[ch * KS + j];
@@ -253,6 +286,7 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
   }
   {
     NEED(w, "project_down.weight"); NEED(b, "project_down.bias");
+    FY_SHAPE(w, 8, D);
     FY_TRY(upload_f32(p, w, 8 * D, &p->pd_w));
     FY_TRY(upload_f32(p, b, 8, &p->pd_b));
   }
@@ -279,8 +313,14 @@ int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* t, int n, const fy_s3_config* cf
       FY_TRY(dev_upload(p, hs, &p->rope_sin));
     }
   }
+  FY_CUDA(cudaDeviceSynchronize());
+  if (p->stage) { cudaFree(p->stage); p->stage = nullptr; p->stage_cap = 0; }
   FY_CUDA(cudaFuncSetAttribute(attn_tc::attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                attn_tc::kSmemBytes));
+  FY_CUDA(cudaFuncSetAttribute(attn_pp::attention_pp_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               attn_pp::smem_bytes<1>()));
+  FY_CUDA(cudaFuncSetAttribute(attn_pp::attention_pp_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               attn_pp::smem_bytes<2>()));
   p->attn_configured = true;
   FY_CUDA(cudaFuncSetAttribute(attn::attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                attn::smem_bytes<true>()));
@@ -405,19 +445,31 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   FY_TRY(make_tmap_bf16(&m_att, b_att, Rtok, D * W, D * W, 128));
   FY_TRY(make_tmap_bf16(&m_h, b_h, Rtok, F * W, F * W, 128));
   FY_CHECK(D == 1280, FY_ERR_ARG, "layernorm kernel is instantiated for d_model == 1280 only (got %d)", D);
-  // tcgen05 attention (split-bf16 only; FY_ATTN_TC=0 falls back to the mma.sync kernel): TMA views of k, v and the
-  // 128-row tile list
-  static const bool attn_tc_env = [] { const char* e = getenv("FY_ATTN_TC"); return !(e && e[0] == '0'); }();
-  const bool attn_tc_on = attn_tc_env && W == 2 && cf.d_model / cf.n_head == 64 && cf.n_head % attn_tc::kHeadsPerCta == 0;
+  // Attention kernel: 2 (default) = two-group ping-pong tcgen05 kernel (both precisions), 1 = the single-group tcgen05
+  // kernel (split-bf16 only), 0 = mma.sync.  TMA views of k, v and the 128-row tile list are shared by the two tcgen05
+  // kernels.
+  static const int attn_env = [] { const char* e = getenv("FY_ATTN_TC"); return e ? atoi(e) : 2; }();
+  const bool heads_ok = cf.d_model / cf.n_head == 64 && cf.n_head % 4 == 0;
+  const bool attn_pp_on = attn_env >= 2 && heads_ok;
+  const bool attn_tc_on = attn_env == 1 && W == 2 && heads_ok;
+  static const float attn_slack = [] { const char* e = getenv("FY_ATTN_SLACK"); return e ? (float)atof(e) : attn_tc::kRescaleSlack; }();
   attn_tc::Params tc_params;
+  attn_pp::Params pp_params;
   if (attn_tc_on) {
     FY_TRY(make_tmap_bf16(&tc_params.tm_kv, b_k, Rtok, D * W, D * W, 64));
     FY_TRY(make_tmap_bf16(&tc_params.tm_v, b_v, Rtok, D * W, D * W, 64));
     tc_params.q = b_q; tc_params.out = b_att; tc_params.ld = D * W; tc_params.lo_off = D; tc_params.rows = Rtok;
-    static const float attn_slack = [] { const char* e = getenv("FY_ATTN_SLACK"); return e ? (float)atof(e) : attn_tc::kRescaleSlack; }();
     tc_params.slack = attn_slack;
     tc_params.tiles = reinterpret_cast<const int2*>(d_meta + lay.m_tiles128);
     tc_params.utt_P = d_P; tc_params.utt_L = d_L;
+  }
+  if (attn_pp_on) {
+    FY_TRY(make_tmap_bf16(&pp_params.tm_k, b_k, Rtok, D * W, D * W, 64));
+    FY_TRY(make_tmap_bf16(&pp_params.tm_v, b_v, Rtok, D * W, D * W, 64));
+    pp_params.q = b_q; pp_params.out = b_att; pp_params.ld = D * W; pp_params.lo_off = D; pp_params.rows = Rtok;
+    pp_params.slack = attn_slack;
+    pp_params.tiles = reinterpret_cast<const int2*>(d_meta + lay.m_tiles128);
+    pp_params.utt_P = d_P; pp_params.utt_L = d_L;
   }
   const float qk_scale = powf(64.0f, -0.25f);
   const int ln_grid = (Rtok + 7) / 8;
@@ -440,7 +492,14 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       if (W == 2) s3k::fsmn_kernel<31, true><<<fg, 128, 0, st>>>(b_v, D * W, D, d_tiles, d_P, d_L, Lw.fsmn, D, b_x);
       else s3k::fsmn_kernel<31, false><<<fg, 128, 0, st>>>(b_v, D * W, D, d_tiles, d_P, d_L, Lw.fsmn, D, b_x);
     }
-    if (attn_tc_on) {
+    if (attn_pp_on) {
+      const int pi = prof_begin(c, PK_ATTN);
+      dim3 grid(tiles128, cf.n_head / attn_pp::kHeadsPerCta);
+      if (W == 2) attn_pp::attention_pp_kernel<2><<<grid, attn_pp::kThreads, attn_pp::smem_bytes<2>(), st>>>(pp_params);
+      else attn_pp::attention_pp_kernel<1><<<grid, attn_pp::kThreads, attn_pp::smem_bytes<1>(), st>>>(pp_params);
+      prof_end(c, pi, attn_flops);
+      c->launches += 4;
+    } else if (attn_tc_on) {
       const int pi = prof_begin(c, PK_ATTN);
       dim3 grid(tiles128, cf.n_head / attn_tc::kHeadsPerCta);
       attn_tc::attention_tc_kernel<<<grid, attn_tc::kThreads, attn_tc::kSmemBytes, st>>>(tc_params);
@@ -490,6 +549,16 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
 }  // extern "C"
 
 #ifdef FY_STALLPROF
+// Debug build only: the ping-pong attention kernel's counters (32 x u64).
+extern "C" int fy_debug_pp_stalls(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  if (cudaMemcpyFromSymbol(out, fy::attn_pp::g_pp_stall, sizeof(unsigned long long) * 32) != cudaSuccess) return 1;
+  if (reset) {
+    unsigned long long z[32] = {0};
+    if (cudaMemcpyToSymbol(fy::attn_pp::g_pp_stall, z, sizeof(z)) != cudaSuccess) return 1;
+  }
+  return 0;
+}
 // Debug build only: copy the attention role-stall counters to the host (16 x u64) and optionally clear them.
 extern "C" int fy_debug_attn_stalls(unsigned long long* out, int reset) {
   cudaDeviceSynchronize();

@@ -68,6 +68,10 @@ class Engine:
         self.h = h
         self._ws = None
         self.s3_cfg = None
+        # offsets arrays already on the device, keyed by their bytes: filled by an eager run, so that the same call
+        # sequence can then be captured in a CUDA graph without any host-to-device copy (frontend.py, batch-1 twin)
+        self.cache_offsets = False
+        self._off_cache = {}
         self.use_stream(torch.cuda.current_stream(self.device))
 
     def close(self):
@@ -86,7 +90,16 @@ class Engine:
 
     # ------------------------------------------------------------------ helpers
     def _dev_i32(self, a: np.ndarray) -> torch.Tensor:
-        return torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to(self.device, non_blocking=True)
+        a = np.ascontiguousarray(a, dtype=np.int32)
+        if not self.cache_offsets:
+            return torch.from_numpy(a).to(self.device, non_blocking=True)
+        key = a.tobytes()
+        t = self._off_cache.get(key)
+        if t is None:
+            if len(self._off_cache) >= 256:
+                self._off_cache.pop(next(iter(self._off_cache)))
+            t = self._off_cache[key] = torch.from_numpy(a).to(self.device)
+        return t
 
     def workspace(self, nbytes: int) -> torch.Tensor:
         if self._ws is None or self._ws.numel() < nbytes:

@@ -78,7 +78,7 @@ class PinnedRing:
     after its last copy, so a slot is never rewritten while the DMA that reads it may still be queued (the copy runs on
     a side stream under the previous batch's kernels; the caller's stream waits for it)."""
 
-    def __init__(self, device: torch.device, slots: int = 3):
+    def __init__(self, device: torch.device, slots: int = 4):
         self.device = device
         self.slots: List[Optional[torch.Tensor]] = [None] * slots
         self.events: List[Optional[torch.cuda.Event]] = [None] * slots
@@ -86,12 +86,8 @@ class PinnedRing:
         self.stream: Optional[torch.cuda.Stream] = None
         self.pack_seconds = 0.0
 
-    def upload(self, arrays: Sequence[np.ndarray], total: int) -> torch.Tensor:
-        """Concatenate 1-D int16 arrays into the next slot and start its copy; returns the device tensor, which the
-        current stream may use (it waits for the copy)."""
-        t0 = time.perf_counter()
-        if self.stream is None:
-            self.stream = torch.cuda.Stream(self.device)
+    def acquire(self, total: int):
+        """Next slot (after its previous copy has finished), grown to `total` samples: (slot index, int16 numpy view)."""
         i = self.k % len(self.slots)
         self.k += 1
         if self.events[i] is not None:
@@ -99,17 +95,31 @@ class PinnedRing:
         if self.slots[i] is None or self.slots[i].numel() < total:
             self.slots[i] = None
             self.slots[i] = torch.empty(max(int(total * 1.25), 1 << 16), dtype=torch.int16).pin_memory()
-        pin = self.slots[i][:total]
-        if arrays:
-            np.concatenate(arrays, out=pin.numpy())
+        return i, self.slots[i][:total].numpy()
+
+    def submit(self, i: int, total: int) -> torch.Tensor:
+        """Start the host->device copy of slot i's first `total` samples on the side stream; the current stream waits
+        for it.  Returns the device tensor."""
+        if self.stream is None:
+            self.stream = torch.cuda.Stream(self.device)
         main = torch.cuda.current_stream(self.device)
         with torch.cuda.stream(self.stream):
-            dev = pin.to(self.device, non_blocking=True)
+            dev = self.slots[i][:total].to(self.device, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self.stream)
         self.events[i] = ev
         main.wait_event(ev)
         dev.record_stream(main)
+        return dev
+
+    def upload(self, arrays: Sequence[np.ndarray], total: int) -> torch.Tensor:
+        """Concatenate 1-D int16 arrays into the next slot and start its copy; returns the device tensor, which the
+        current stream may use (it waits for the copy)."""
+        t0 = time.perf_counter()
+        i, view = self.acquire(total)
+        if arrays:
+            np.concatenate(arrays, out=view)
+        dev = self.submit(i, total)
         self.pack_seconds += time.perf_counter() - t0
         return dev
 
@@ -163,7 +173,10 @@ class Extractor:
     # ------------------------------------------------------------------ stage 1
     def embed_batch(self, utts: Sequence[Utt]) -> torch.Tensor:
         """[n, 192] fp32 on the device for one batch."""
-        pcm, lens = self._to_device_16k(utts, "first")
+        return self.embed_pcm(*self._to_device_16k(utts, "first"))
+
+    def embed_pcm(self, pcm: torch.Tensor, lens: Sequence[int]) -> torch.Tensor:
+        """Stage 1 on packed mono 16 kHz PCM already on the device (int16 or float32)."""
         for i, n in enumerate(lens):
             if kaldi_num_frames(n) < 3:
                 raise ValueError(f"utterance {i} of the batch is too short for CAMPPlus ({n} samples at 16 kHz)")
@@ -289,7 +302,10 @@ class Extractor:
     # ------------------------------------------------------------------ stage 2
     def tokenize_batch(self, utts: Sequence[Utt]):
         """(packed int32 tokens on the device, token counts) for one batch; every utterance must pass the gate."""
-        pcm, lens = self._to_device_16k(utts, "mean")
+        return self.tokenize_pcm(*self._to_device_16k(utts, "mean"))
+
+    def tokenize_pcm(self, pcm: torch.Tensor, lens: Sequence[int]):
+        """Stage 2 on packed mono 16 kHz PCM already on the device: (packed int32 tokens, token counts)."""
         mel, frames = self.eng.logmel(pcm, lens)
         return self.eng.s3tok(mel, frames)
 

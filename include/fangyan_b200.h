@@ -82,6 +82,34 @@ const char* fy_version(void);
 int fy_load_campplus(fy_ctx* ctx, const fy_tensor* h_tensors, int n, const fy_campplus_config* cfg);
 int fy_load_s3tok(fy_ctx* ctx, const fy_tensor* h_tensors, int n, const fy_s3_config* cfg);
 
+/* ---- A1 / N2: torchaudio.load(path) for RIFF/WAVE files, on the HOST (no device work, no ctx) -------------------
+ * tools/extract_embedding.py:26, tools/extract_speech_token.py:28, cosyvoice/utils/file_utils.py:45.
+ * fy_wav_scan parses n headers with n_threads plain threads: frames, channels, rate, sample format and the byte
+ * offset of the samples (what the host needs to plan batches before decoding anything); a file that cannot be opened
+ * or is not RIFF/WAVE gets a negative status in ITS record, the call still returns FY_OK.
+ * fy_wav_read_s16 copies n_samples[i] int16 values starting at data_offset[i] of file i into dst[i] -- host memory
+ * of the caller, typically slices of a pinned staging buffer so the samples go page cache -> pinned -> GPU with one
+ * copy on the host.  Interleaved channels are copied as they are (pass frames * channels).  On failure returns
+ * FY_ERR_ARG, names the file in fy_last_error() and stores its index in *bad_index (may be NULL). */
+typedef enum {
+  FY_WAV_OK = 0,
+  FY_WAV_ERR_OPEN = -1,         /* cannot open / read */
+  FY_WAV_ERR_FORMAT = -2,       /* not RIFF/WAVE */
+  FY_WAV_ERR_LONG_HEADER = -3   /* no fmt + data chunk within the first 4 KiB: needs a full parse */
+} fy_wav_status;
+typedef struct {
+  int64_t frames;        /* samples per channel */
+  int64_t data_offset;   /* byte offset of the first sample */
+  int32_t channels, sample_rate;
+  int32_t format;        /* 1 = integer PCM, 3 = IEEE float (WAVE_FORMAT_EXTENSIBLE resolved to its sub-format) */
+  int32_t bits;          /* bits per sample */
+  int32_t status;        /* fy_wav_status */
+  int32_t reserved;
+} fy_wav_info;
+int fy_wav_scan(const char* const* paths, int n, fy_wav_info* out, int n_threads);
+int fy_wav_read_s16(const char* const* paths, const int64_t* data_offset, const int64_t* n_samples, int16_t* const* dst,
+                    int n, int n_threads, int32_t* bad_index);
+
 /* ---- A2: torchaudio.transforms.Resample(orig, 16000) ------------------------------------------------------
  * tools/extract_embedding.py:27-28, tools/extract_speech_token.py:29-30, cosyvoice/utils/file_utils.py:47-49.
  * One launch resamples a packed batch that shares one input rate.  Output length per utterance is

@@ -218,3 +218,28 @@ def test_twin_loads_exporter_style_onnx(data_dir, tmp_path):
     assert float(torch.nn.functional.cosine_similarity(ea, eb, dim=0)) >= 0.99999     # folding moves rounding only
     ta, tb = a._extract_speech_token(wav)[0].cpu(), b._extract_speech_token(wav)[0].cpu()
     assert torch.equal(ta, tb)                                                         # same weights bit for bit
+
+
+def test_twin_cuda_graph_replay_is_bit_identical(data_dir, tmp_path):
+    """B2 latency path: the captured launch sequence of a prompt length gives the same bits as the eager calls, for the
+    prompt it was captured on and for a different prompt of the same length (replay with new input)."""
+    import os
+    from fangyan_tts_b200.frontend import CosyVoiceFrontEndB200
+    d, keys, utts, st = data_dir
+    rng = np.random.default_rng(8)
+    a, b = synth.utterance(rng, 2.5), synth.utterance(rng, 2.5)
+    synth.write_wav(tmp_path / "a.wav", a)
+    synth.write_wav(tmp_path / "b.wav", b)
+    os.environ["FY_S3TOK_CONFIG"] = str(d / "s3.json")
+    try:
+        eager = CosyVoiceFrontEndB200(str(d / "campplus.npz"), str(d / "s3tok.npz"), use_graphs=False)
+        graph = CosyVoiceFrontEndB200(str(d / "campplus.npz"), str(d / "s3tok.npz"), use_graphs=True)
+    finally:
+        del os.environ["FY_S3TOK_CONFIG"]
+    for name in ("a", "b", "a", "b"):                 # first a: eager warm-up + capture; then three replays
+        wav = str(tmp_path / f"{name}.wav")
+        assert torch.equal(graph._extract_spk_embedding(wav), eager._extract_spk_embedding(wav)), name
+        tg, lg = graph._extract_speech_token(wav)
+        te, le = eager._extract_speech_token(wav)
+        assert torch.equal(tg, te) and torch.equal(lg, le), name
+    assert len(graph._graphs) == 2                    # one graph per (method, length)

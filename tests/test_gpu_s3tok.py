@@ -77,9 +77,9 @@ from fangyan_tts_b200 import synth, synth_weights
 from fangyan_tts_b200.configs import S3Config
 from fangyan_tts_b200.engine import Engine
 cfg = S3Config(n_layer=2)
-eng = Engine(0, "bf16x3")
+eng = Engine(0, sys.argv[2])
 eng.load_s3tok(synth_weights.s3tok_state(cfg, seed=5), cfg)
-utts = synth.make_set(12, 23, 0.3, 9.0)
+utts = synth.make_set(12, 23, 0.3, 9.0) + synth.make_set(2, 29, 25.0, 30.0)
 lens = [len(u) for u in utts]
 pcm = torch.from_numpy(np.concatenate(utts)).cuda()
 mel, frames = eng.logmel(pcm, lens)
@@ -89,32 +89,48 @@ print(json.dumps({"tok": tok.cpu().tolist(), "counts": list(counts), "pre": pre.
 """
 
 
-def test_both_attention_kernels_agree():
-    """The tcgen05 kernel (default) and the mma.sync kernel (FY_ATTN_TC=0) compute the same attention: pre-FSQ
-    activations within 2e-4 of each other, token ids >= 99.9 % equal, counts bit-exact.  The switch is read once per
-    process, so each kernel runs in its own interpreter."""
+def _attention_variant(prec, env_extra):
     import json
     import os
     import subprocess
     import sys
     from pathlib import Path
-
     root = str(Path(__file__).resolve().parent.parent)
-    out = {}
-    for v in ("1", "0", "slack0"):
-        # "slack0": tcgen05 kernel with no slack on the running maximum, i.e. O is rescaled in tensor memory whenever a
-        # tile raises the row maximum (the default 2^8 slack makes that path rare)
-        env = dict(os.environ, FY_ATTN_TC="1", FY_ATTN_SLACK="0") if v == "slack0" else dict(os.environ, FY_ATTN_TC=v)
-        r = subprocess.run([sys.executable, "-c", _ALT_ATTENTION, root], env=env, capture_output=True, text=True, timeout=600)
-        assert r.returncode == 0, r.stderr[-2000:]
-        out[v] = json.loads(r.stdout.strip().splitlines()[-1])
-    assert out["1"]["counts"] == out["0"]["counts"]
-    a, b = np.asarray(out["1"]["pre"]), np.asarray(out["0"]["pre"])
-    assert a.shape == b.shape and np.isfinite(a).all()
-    assert float(np.abs(a - b).max()) <= 2e-4
-    ta, tb = np.asarray(out["1"]["tok"]), np.asarray(out["0"]["tok"])
-    assert float((ta == tb).mean()) >= 0.999
-    c = np.asarray(out["slack0"]["pre"])
-    assert out["slack0"]["counts"] == out["1"]["counts"] and np.isfinite(c).all()
-    assert float(np.abs(a - c).max()) <= 2e-4
-    assert float((np.asarray(out["slack0"]["tok"]) == ta).mean()) >= 0.999
+    r = subprocess.run([sys.executable, "-c", _ALT_ATTENTION, root, prec], env=dict(os.environ, **env_extra),
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def test_all_attention_kernels_agree():
+    """The three attention kernels compute the same attention in the parity mode: the two-group ping-pong tcgen05 kernel
+    (default, FY_ATTN_TC=2), the single-group tcgen05 kernel (=1) and the mma.sync kernel (=0): pre-FSQ activations
+    within 2e-4 of each other, token ids >= 99.9 % equal, counts bit-exact -- also with no slack on the running
+    maximum (O rescaled in tensor memory whenever a tile raises the row maximum; the default 2^8 slack makes that path
+    rare).  Clips from 0.3 to 30 s: 1 to 12 key tiles per head.  The switch is read once per process, so each kernel
+    runs in its own interpreter."""
+    out = {v: _attention_variant("bf16x3", {"FY_ATTN_TC": v}) for v in ("2", "1", "0")}
+    out["pp_slack0"] = _attention_variant("bf16x3", {"FY_ATTN_TC": "2", "FY_ATTN_SLACK": "0"})
+    out["tc_slack0"] = _attention_variant("bf16x3", {"FY_ATTN_TC": "1", "FY_ATTN_SLACK": "0"})
+    ref = out["0"]
+    a = np.asarray(ref["pre"])
+    ta = np.asarray(ref["tok"])
+    assert np.isfinite(a).all()
+    for name in ("2", "1", "pp_slack0", "tc_slack0"):
+        o = out[name]
+        assert o["counts"] == ref["counts"], name
+        b = np.asarray(o["pre"])
+        assert b.shape == a.shape and np.isfinite(b).all(), name
+        assert float(np.abs(a - b).max()) <= 2e-4, (name, float(np.abs(a - b).max()))
+        assert float((np.asarray(o["tok"]) == ta).mean()) >= 0.999, name
+
+
+def test_bf16_mode_attention_is_tcgen05_and_agrees_with_mma_sync():
+    """the single-pass bf16 encoder mode (BASELINE configs[3]) used to fall back to mma.sync attention.  It
+    now runs the ping-pong tcgen05 kernel (W = 1); both kernels round P and the operands to bf16 once, so they agree to
+    bf16 accuracy, far inside what separates this mode from the fp32 oracle (pre-FSQ error ~2e-2)."""
+    a, b = _attention_variant("bf16", {"FY_ATTN_TC": "2"}), _attention_variant("bf16", {"FY_ATTN_TC": "0"})
+    assert a["counts"] == b["counts"]
+    x, y = np.asarray(a["pre"]), np.asarray(b["pre"])
+    assert np.isfinite(x).all() and float(np.abs(x - y).max()) <= 3e-2
+    assert float((np.asarray(a["tok"]) == np.asarray(b["tok"])).mean()) >= 0.97

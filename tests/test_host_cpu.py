@@ -124,6 +124,44 @@ def test_read_wav_fails_loudly_with_key(tmp_path):
         kaldi_io.wav_header(str(p), "utt_42")
 
 
+def test_native_scan_and_direct_read_agree_with_the_python_reader(tmp_path):
+    """Rows A1 / N2: fy_wav_scan + fy_wav_read_s16 (host threads in the library) against audio_io.read_wav, over the
+    header variants of _riff (junk chunk before fmt, extensible), other encodings (flagged not-simple) and errors."""
+    pcm = synth.make_set(6, 4, 0.05, 0.4)
+    keys = synth.write_kaldi_dir(tmp_path, pcm)
+    paths = [str(tmp_path / "wav" / f"{k}.wav") for k in keys]
+    v = np.array([0, 1000, -1000, 32767, -32768], dtype=np.int16)
+    extra = {"ext": _riff(1, 1, 16000, 16, v.tobytes(), extensible=True),
+             "f32": _riff(3, 1, 16000, 32, (v.astype(np.float32) / 32768.0).astype("<f4").tobytes()),
+             "st24k": _riff(1, 2, 24000, 16, np.stack([v, -v], 1).tobytes()),
+             "cut": _riff(1, 1, 16000, 16, v.tobytes())[:-4]}                 # data chunk longer than the file
+    for name, blob in extra.items():
+        (tmp_path / f"{name}.wav").write_bytes(blob)
+        keys.append(name)
+        paths.append(str(tmp_path / f"{name}.wav"))
+    sc = audio_io.scan_wavs(keys, paths, 3)
+    for i, (k, p) in enumerate(zip(keys, paths)):
+        x, sr = audio_io.read_wav(p, k)
+        assert (int(sc["frames"][i]), int(sc["channels"][i]), int(sc["sample_rate"][i])) == (x.shape[0], x.shape[1], sr), k
+        assert kaldi_io.wav_header(p, k) == (x.shape[0], x.shape[1], sr)
+    assert sc["simple"].tolist() == [True] * 6 + [True, False, True, True]
+    idx = [8, 3, 6, 0, 9]                                                    # stereo file: interleaved as stored
+    dst = np.zeros(int((sc["frames"][idx] * sc["channels"][idx]).sum()), np.int16)
+    audio_io.read_s16_into(sc, idx, dst, 2, keys)
+    want = np.concatenate([audio_io.read_wav(paths[i])[0].reshape(-1) for i in idx])
+    assert np.array_equal(dst, want)
+    (tmp_path / "bad.wav").write_bytes(b"ID3" + b"\x00" * 80)
+    with pytest.raises(audio_io.AudioDecodeError, match="k_bad"):
+        audio_io.scan_wavs(["k_bad"], [str(tmp_path / "bad.wav")], 1)
+    with pytest.raises(audio_io.AudioDecodeError, match="k_gone"):
+        audio_io.scan_wavs(["k_gone"], [str(tmp_path / "gone.wav")], 1)
+    big = _riff(1, 1, 16000, 16, v.tobytes())                                # data chunk beyond the first 4 KiB
+    big = big[:12] + b"LIST" + struct.pack("<I", 5000) + b"\x00" * 5000 + big[12:]
+    (tmp_path / "long.wav").write_bytes(big)
+    sl = audio_io.scan_wavs(["long"], [str(tmp_path / "long.wav")], 1)
+    assert int(sl["frames"][0]) == 5 and not sl["simple"][0]                # parsed by the Python reader, not direct
+
+
 # ---------------------------------------------------------------------------------------- Kaldi tables + outputs
 def test_kaldi_dir_round_trip_and_table_parsing(tmp_path):
     utts = synth.make_set(5, 9, 0.1, 0.3)
