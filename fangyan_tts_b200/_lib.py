@@ -15,7 +15,7 @@ class FyTensor(C.Structure):
 
 class FyS3Config(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("n_mels", "d_model", "n_head", "n_layer", "d_ff", "fsmn_kernel", "fsq_dim")] + \
-               [(n, C.c_float) for n in ("rope_theta", "ln_eps", "fsq_scale")]
+               [(n, C.c_float) for n in ("rope_theta", "ln_eps", "fsq_scale", "mlp_ln_eps")]
 
 
 class FyCamConfig(C.Structure):

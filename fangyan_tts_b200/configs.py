@@ -40,7 +40,8 @@ class S3Config:
     fsq_dim: int = 8
     fsq_levels: int = 3
     rope_theta: float = 10000.0
-    ln_eps: float = 1e-5
+    ln_eps: float = 1e-5            # attention LayerNorm (and the MLP one unless mlp_ln_eps is set)
+    mlp_ln_eps: float | None = None  # the two norms of a block may carry different epsilons in the real graph (UNVERIFIED)
     fsq_scale: float = 0.9990000128746033
 
     @property

@@ -111,7 +111,7 @@ __device__ unsigned long long g_pp_stall[32];
 #endif
 
 template <int W>
-__global__ void __maxnreg__(200) attention_pp_kernel(const __grid_constant__ Params p) {
+__global__ void __maxnreg__(168) attention_pp_kernel(const __grid_constant__ Params p) {
   constexpr int kStages = stages<W>();
   constexpr int kStageBytes = stage_bytes<W>();
   extern __shared__ uint8_t smem_raw[];

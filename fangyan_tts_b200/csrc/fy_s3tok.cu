@@ -521,8 +521,9 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
       g.epi.mode = EPI_F32_ADD; g.epi.out = b_x; g.epi.ldo = D; g.epi.bias = Lw.bo;
       FY_TRY(run_gemm(c, g, 2.0 * vtok * D * D));
     }
-    if (W == 2) s3k::layernorm_kernel<true, 1280><<<ln_grid, 256, 0, st>>>(b_x, Lw.ln2_g, Lw.ln2_b, cf.ln_eps, Rtok, b_xn);
-    else s3k::layernorm_kernel<false, 1280><<<ln_grid, 256, 0, st>>>(b_x, Lw.ln2_g, Lw.ln2_b, cf.ln_eps, Rtok, b_xn);
+    const float eps2 = cf.mlp_ln_eps > 0.f ? cf.mlp_ln_eps : cf.ln_eps;
+    if (W == 2) s3k::layernorm_kernel<true, 1280><<<ln_grid, 256, 0, st>>>(b_x, Lw.ln2_g, Lw.ln2_b, eps2, Rtok, b_xn);
+    else s3k::layernorm_kernel<false, 1280><<<ln_grid, 256, 0, st>>>(b_x, Lw.ln2_g, Lw.ln2_b, eps2, Rtok, b_xn);
     {
       GemmArgs g;
       g.tmap_a = m_xn; g.tmap_b = Lw.m_1; g.M = Rtok; g.N = F;

@@ -153,7 +153,7 @@ class Engine:
         check_shapes(state, "s3tok", cfg)
         arr, keep = self._tensor_table(state)
         c = FyS3Config(cfg.n_mels, cfg.d_model, cfg.n_head, cfg.n_layer, cfg.d_ff, cfg.fsmn_kernel, cfg.fsq_dim,
-                       cfg.rope_theta, cfg.ln_eps, cfg.fsq_scale)
+                       cfg.rope_theta, cfg.ln_eps, cfg.fsq_scale, cfg.mlp_ln_eps if cfg.mlp_ln_eps is not None else 0.0)
         check(self.lib.fy_load_s3tok(self.h, arr, len(state), C.byref(c)))
         self.s3_cfg = cfg
 

@@ -410,9 +410,10 @@ def s3tok_from_onnx(path, cfg) -> Dict[str, np.ndarray]:
 
     def lnorm(unit, name):
         w = wk.take(unit, "LayerNorm", c=d)
-        if abs(w.extra["eps"] - cfg.ln_eps) > 1e-12:
+        want = cfg.ln_eps if name.endswith("attn_ln") or cfg.mlp_ln_eps is None else cfg.mlp_ln_eps
+        if abs(w.extra["eps"] - want) > 1e-12:
             raise OnnxStructureError(f"{path}: {unit} has epsilon {w.extra['eps']:g}, the hyper-parameter table says "
-                                     f"{cfg.ln_eps:g} (set ln_eps through FY_S3TOK_CONFIG)")
+                                     f"{want:g} (set ln_eps / mlp_ln_eps through FY_S3TOK_CONFIG)")
         st[name + ".weight"], st[name + ".bias"] = np.asarray(w.extra["scale"], np.float32), np.asarray(w.extra["bias"], np.float32)
 
     conv("conv1", "conv1", (d, cfg.n_mels, 3))

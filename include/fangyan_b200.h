@@ -59,6 +59,7 @@ typedef struct {
 typedef struct {
   int32_t n_mels, d_model, n_head, n_layer, d_ff, fsmn_kernel, fsq_dim;
   float rope_theta, ln_eps, fsq_scale;
+  float mlp_ln_eps;    /* epsilon of the MLP LayerNorm when it differs from the attention one (ln_eps); <= 0: same */
 } fy_s3_config;
 
 /* Hyper-parameters of CAMPPlus (UNVERIFIED against the real ONNX graph). */

@@ -10,7 +10,7 @@ callees the reference uses, where they import in the build container:
   * resample         <-> torchaudio.transforms.Resample       (same)
   * whisper_log_mel  <-> transformers.WhisperFeatureExtractor (openai-whisper is absent:
                          "parity unpinned" against whisper itself)
-tests/test_oracle_frontend.py performs those checks when the libraries import.
+tests/test_oracle_cpu.py performs those checks when the libraries import.
 
 Reference call sites restated here (paths relative to /root/reference/CosyVoice):
   tools/extract_embedding.py:26-33       load -> resample -> kaldi.fbank(80, dither=0) -> CMN

@@ -33,7 +33,8 @@ class S3Config:
     fsq_dim: int = 8
     fsq_levels: int = 3
     rope_theta: float = 10000.0
-    ln_eps: float = 1e-5
+    ln_eps: float = 1e-5            # attention LayerNorm (and the MLP one unless mlp_ln_eps is set)
+    mlp_ln_eps: float | None = None  # the two norms of a block may carry different epsilons in the real graph (UNVERIFIED)
     fsq_scale: float = 0.9990000128746033
 
     @property
@@ -105,7 +106,7 @@ class Block(nn.Module):
         d = cfg.d_model
         self.attn_ln = nn.LayerNorm(d, eps=cfg.ln_eps)
         self.attn = FsmnAttention(cfg)
-        self.mlp_ln = nn.LayerNorm(d, eps=cfg.ln_eps)
+        self.mlp_ln = nn.LayerNorm(d, eps=cfg.ln_eps if cfg.mlp_ln_eps is None else cfg.mlp_ln_eps)
         self.fc1 = nn.Linear(d, cfg.d_ff)
         self.fc2 = nn.Linear(cfg.d_ff, d)
 

@@ -151,9 +151,10 @@ def write_campplus(path, st, cfg, fold=True, drop_layer=None, dense_as_gemm=Fals
     g.save(path)
 
 
-def write_s3tok(path, st, cfg, ln_eps=None, swap_kv=False):
+def write_s3tok(path, st, cfg, ln_eps=None, swap_kv=False, mlp_ln_eps=None):
     g, d = Graph(), cfg.d_model
     eps = float(cfg.ln_eps if ln_eps is None else ln_eps)
+    eps2 = float(eps if mlp_ln_eps is None else mlp_ln_eps)
 
     def linear(x, name, orig, bias=True):
         y = g.node("MatMul", [x, g.init(g.fresh("onnx::MatMul"), np.ascontiguousarray(st[name + ".weight"].T))])
@@ -190,7 +191,7 @@ def write_s3tok(path, st, cfg, ln_eps=None, swap_kv=False):
         a = linear(g.node("MatMul", [w, v]), p + "attn.out", o + "attn.out")
         x = g.node("Add", [x, g.node("Add", [a, mem])])
         h = g.node("LayerNormalization", [x, g.init(o + "mlp_ln.weight", st[p + "mlp_ln.weight"]),
-                                          g.init(o + "mlp_ln.bias", st[p + "mlp_ln.bias"])], axis=-1, epsilon=eps)
+                                          g.init(o + "mlp_ln.bias", st[p + "mlp_ln.bias"])], axis=-1, epsilon=eps2)
         x = g.node("Add", [x, linear(gelu(linear(h, p + "fc1", o + "mlp.0")), p + "fc2", o + "mlp.2")])
     h = g.node("Tanh", [linear(x, "project_down", "quantizer._codebook.project_down")])
     h = g.node("Round", [g.node("Mul", [h, g.init("fsq_scale", np.array(0.999, np.float32))])])

@@ -69,6 +69,22 @@ def test_s3tok_matches_oracle(n_layer, prec, tol):
     eng.close()
 
 
+def test_separate_layernorm_epsilons():
+    """the real graph may use different epsilons for attn_ln and mlp_ln; the ABI carries both.  Exaggerated
+    values so that a kernel using the wrong one would be far outside the tolerance."""
+    cfg = S.S3Config(n_layer=2, ln_eps=1e-6, mlp_ln_eps=0.3)
+    model = S.init_random(S.S3Tokenizer(cfg), seed=77)
+    eng = Engine(0, "bf16x3")
+    eng.load_s3tok(_state(model, cfg), cfg)
+    mels = _mels(synth.make_set(4, 31, 1.0, 4.0))
+    tok, lens, pre = _run(eng, model, mels)
+    ids, pres = _oracle(model, mels)
+    assert float((pre - torch.cat(pres)).abs().max()) <= 2e-4
+    same = S.init_random(S.S3Tokenizer(S.S3Config(n_layer=2, ln_eps=1e-6)), seed=77)       # one epsilon: different network
+    assert float((torch.cat(_oracle(same, mels)[1]) - torch.cat(pres)).abs().max()) > 1e-2
+    eng.close()
+
+
 _ALT_ATTENTION = r"""
 import json, sys
 import numpy as np, torch

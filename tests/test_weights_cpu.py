@@ -44,6 +44,11 @@ def test_s3tok_onnx_structure_errors_are_structural(tmp_path):
         weights.load_state(tmp_path / "c.onnx", "s3tok", cfg)
     got = weights.load_state(tmp_path / "c.onnx", "s3tok", S3Config(**{**SMALL_S3, "ln_eps": 1e-6}))
     assert np.array_equal(got["blocks.1.fc2.weight"], st["blocks.1.fc2.weight"])
+    # the two norms of a block may carry different epsilons: the table has one field for each
+    OW.write_s3tok(tmp_path / "d.onnx", st, cfg, ln_eps=1e-6, mlp_ln_eps=1e-5)
+    with pytest.raises(weights.OnnxStructureError, match=r"mlp_ln has epsilon 1e-05"):
+        weights.load_state(tmp_path / "d.onnx", "s3tok", S3Config(**{**SMALL_S3, "ln_eps": 1e-6}))
+    weights.load_state(tmp_path / "d.onnx", "s3tok", S3Config(**{**SMALL_S3, "ln_eps": 1e-6, "mlp_ln_eps": 1e-5}))
 
 
 def _cam(state):
