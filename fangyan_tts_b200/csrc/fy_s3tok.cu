@@ -466,6 +466,7 @@ int fy_s3tok_encode_fsq(fy_ctx* ctx, const float* mel, const int32_t* frame_off,
   if (attn_pp_on) {
     FY_TRY(make_tmap_bf16(&pp_params.tm_k, b_k, Rtok, D * W, D * W, 64));
     FY_TRY(make_tmap_bf16(&pp_params.tm_v, b_v, Rtok, D * W, D * W, 64));
+    FY_TRY(make_tmap_bf16(&pp_params.tm_q, b_q, Rtok, D * W, D * W, 128));
     pp_params.q = b_q; pp_params.out = b_att; pp_params.ld = D * W; pp_params.lo_off = D; pp_params.rows = Rtok;
     pp_params.slack = attn_slack;
     pp_params.tiles = reinterpret_cast<const int2*>(d_meta + lay.m_tiles128);

@@ -66,7 +66,9 @@ __device__ __forceinline__ void mma_ts_elect(uint32_t d, uint32_t a, uint64_t db
       "r"(a), "l"(db), "r"(id), "r"(acc)
       : "memory");
 }
-template <bool CONV, int BUSY>
+// BMN = 1: B is MN-major (the P V product of the attention kernels: V tiles as [key][d] rows), descriptor step 2048 B.
+// BUSY = 2: the other warps run tcgen05.ld / tcgen05.st round trips on their TMEM lane quarters instead of FP32 work.
+template <bool CONV, int BUSY, int BMN = 0>
 __global__ void __launch_bounds__(32 + 32 * 16, 1) issue_kernel(long long* out, int slot, float* sink) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -81,14 +83,15 @@ __global__ void __launch_bounds__(32 + 32 * 16, 1) issue_kernel(long long* out, 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = holder;
-  constexpr uint32_t id = idesc(128, 64);
+  constexpr uint32_t id = idesc(128, 64) | (BMN ? (1u << 16) : 0u);
   constexpr int kIters = 384;
+  constexpr int kStep = BMN ? 128 : 2;
   if (threadIdx.x < 32) {
     const uint64_t db = ptx::make_desc_sw128(ptx::smem_u32(smem));
     if (CONV) {
       const long long t0 = clock64();
 #pragma unroll 12
-      for (int i = 0; i < kIters; ++i) mma_ts_elect(tmem + (i / 12 % 3) * 64, tmem + 448 + 8 * (i & 3), db + 2 * (i & 3), id, i % 12 != 0);
+      for (int i = 0; i < kIters; ++i) mma_ts_elect(tmem + (i / 12 % 3) * 64, tmem + 448 + 8 * (i & 3), db + kStep * (i & 3), id, i % 12 != 0);
       if (ptx::elect_one()) ptx::mma_commit(&bar);
       ptx::mbar_wait(&bar, 0);
       if (threadIdx.x == 0) out[slot] = (clock64() - t0) / kIters;
@@ -102,6 +105,18 @@ __global__ void __launch_bounds__(32 + 32 * 16, 1) issue_kernel(long long* out, 
     }
     __syncwarp();
     if (threadIdx.x == 0) done = 1;
+  } else if (BUSY == 2) {
+    const uint32_t t_row = tmem + ((uint32_t)(((threadIdx.x >> 5) & 3) * 32) << 16) + 256 + 16 * ((threadIdx.x >> 7) & 3);
+    uint32_t v[16];
+    while (!done) {
+      ptx::tmem_ld_32x16(t_row, v);
+      ptx::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] += 1;
+      ptx::tmem_st_32x16(t_row, v);
+      ptx::tmem_st_wait();
+    }
+    if (v[0] == 0x12345678u) *sink = 1.f;
   } else if (BUSY) {
     float a = threadIdx.x, b = 1.0001f, c = 0.5f, d = 0.25f;
     while (!done) {
@@ -114,10 +129,10 @@ __global__ void __launch_bounds__(32 + 32 * 16, 1) issue_kernel(long long* out, 
   __syncthreads();
   if (threadIdx.x < 32) { ptx::tc_fence_after(); ptx::tmem_dealloc<512>(tmem); }
 }
-template <bool CONV, int BUSY>
+template <bool CONV, int BUSY, int BMN = 0>
 void run_issue(long long* d_out, int slot, float* sink) {
-  cudaFuncSetAttribute(issue_kernel<CONV, BUSY>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-  issue_kernel<CONV, BUSY><<<1, 32 + 32 * 16, 64 * 1024>>>(d_out, slot, sink);
+  cudaFuncSetAttribute(issue_kernel<CONV, BUSY, BMN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+  issue_kernel<CONV, BUSY, BMN><<<1, 32 + 32 * 16, 64 * 1024>>>(d_out, slot, sink);
 }
 
 template <int N, int NACC, bool TS>
@@ -141,6 +156,8 @@ int main() {
   cudaMalloc(&sink, 4);
   run_issue<false, 0>(d_out, s++, sink); run_issue<false, 1>(d_out, s++, sink);
   run_issue<true, 0>(d_out, s++, sink); run_issue<true, 1>(d_out, s++, sink);
+  run_issue<true, 0, 1>(d_out, s++, sink); run_issue<true, 1, 1>(d_out, s++, sink);
+  run_issue<true, 2, 0>(d_out, s++, sink); run_issue<true, 2, 1>(d_out, s++, sink);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
   long long h[64];
@@ -149,7 +166,9 @@ int main() {
                          "N128 acc1 SS", "N128 acc2 SS", "N128 acc1 TS", "N128 acc2 TS", "N256 acc1 SS", "N256 acc1 TS",
                          "N32 acc1 TS", "N32 acc4 TS"};
   const char* inames[] = {"lane-0 branch, idle SM", "lane-0 branch, 16 busy warps", "converged + elect, idle SM",
-                          "converged + elect, 16 busy warps"};
+                          "converged + elect, 16 busy warps", "converged, B MN-major, idle SM",
+                          "converged, B MN-major, 16 busy warps", "converged, 16 warps of TMEM ld/st",
+                          "converged, B MN-major, TMEM ld/st"};
   for (int i = s_issue; i < s; ++i) printf("N64 TS, 12-long chains, %-34s %lld clk / mma\n", inames[i - s_issue], h[i]);
   s = s_issue;
   for (int i = 0; i < s; ++i) printf("%-14s %lld clk / mma (floor %d)\n", names[i], h[i], 128 * atoi(names[i] + 1) / 256);

@@ -43,13 +43,15 @@ def main():
     assert lib.fy_debug_pp_stalls(buf, 1) == 0
     v = [int(b) for b in buf]
     n_cta = max(v[6], 1)
-    il, sl, pl = max(v[5], 1), max(v[14], 1), max(v[18], 1)
+    il, sl, pl = max(v[5], 1), max(v[14], 1), max(v[18], 1)   # issuer: summed over the two issuing warps
     print(f"{prec} {len(utts)} utts ({'bench workload' if secs <= 0 else str(secs) + ' s clips'}): CTAs*launches={n_cta}  "
-          f"life/CTA: issuer {il / n_cta / 1e3:.1f} softmax {sl / n_cta / 1e3:.1f} producer {pl / n_cta / 1e3:.1f} kclk, "
+          f"life/CTA: issuer {il / n_cta / 2e3:.1f} softmax {sl / n_cta / 1e3:.1f} producer {pl / n_cta / 1e3:.1f} kclk, "
           f"prologue {v[19] / n_cta / 1e3:.2f} kclk")
     print("issuer  : q_full %.1f%% k_full %.1f%% v_full %.1f%% p_full %.1f%% o_empty %.1f%%" % tuple(100.0 * v[i] / il for i in range(5)))
     print("softmax (thread 0): s_full %.1f%% S load %.1f%% max+ex2 %.1f%% pack+store %.1f%% o_full %.1f%% head epilogue %.1f%% Q staging %.1f%%"
           % tuple(100.0 * v[i] / sl for i in (8, 9, 10, 11, 12, 13, 15)))
+    print("  head epilogue: O load %.1f%% normalise+transpose %.1f%% stores %.1f%%;  of max+ex2: mask+max %.1f%%"
+          % tuple(100.0 * v[i] / sl for i in (20, 21, 22, 23)))
     print("producer: k_empty %.1f%% v_empty %.1f%%" % tuple(100.0 * v[i] / pl for i in (16, 17)))
 
 
