@@ -82,6 +82,19 @@ def _dist_env():
     return None
 
 
+def _visible_gpus_fast():
+    """Number of GPUs this process will see, WITHOUT importing torch or creating a CUDA context (both cost seconds):
+    the driver's /proc listing filtered by CUDA_VISIBLE_DEVICES.  None when that cannot be told cheaply."""
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis is not None:
+        ids = [x for x in vis.split(",") if x.strip() != ""]
+        return len(ids) if all(x.strip().lstrip("-").isdigit() or x.strip().startswith(("GPU-", "MIG-")) for x in ids) else None
+    try:
+        return len(os.listdir("/proc/driver/nvidia/gpus")) or None
+    except OSError:
+        return None
+
+
 def _n_gpus() -> int:
     import torch
     if not torch.cuda.is_available():
@@ -110,6 +123,20 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         torch.cuda.set_device(local_rank)
         D.init(rank, world, "nccl", port, torch.device("cuda", local_rank))
     t_start = time.perf_counter()
+    warm = None
+    if world > 1:
+        # NCCL builds its communicator at the first collective (~1.5 s): do that under the weight upload and the header
+        # scan instead of in front of the result gather
+        import threading
+
+        def _warm():
+            torch.cuda.set_device(local_rank)
+            t = torch.zeros(1, device=torch.device("cuda", local_rank))
+            torch.distributed.all_reduce(t)
+            torch.cuda.synchronize()
+
+        warm = threading.Thread(target=_warm, daemon=True)
+        warm.start()
     utt2wav = kaldi_io.read_table(os.path.join(args.dir, "wav.scp"))
     keys, paths = list(utt2wav.keys()), list(utt2wav.values())
     pool = ThreadPoolExecutor(max_workers=max(1, args.num_thread))
@@ -187,6 +214,8 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
     def to_dev(values, dtype):
         return torch.from_numpy(np.asarray(values, dtype=dtype)).to(dev, non_blocking=True)
 
+    if warm is not None:
+        warm.join()
     t_loop = time.perf_counter()
     if stage == 1:
         utt2spk = kaldi_io.read_table(os.path.join(args.dir, "utt2spk"))
@@ -294,14 +323,59 @@ def run_stage(stage: int, argv=None, prog: str = "extract") -> int:
     if env is not None:             # already under torchrun: one rank per process
         _worker(env[2], env[1], stage, args, int(os.environ.get("MASTER_PORT", "29531")), False)
         return 0
-    world = _n_gpus()
+    fast = _visible_gpus_fast()
+    world = max(1, min(fast, int(os.environ.get("FY_GPUS", fast)))) if fast else _n_gpus()
     if world == 1:
+        _n_gpus()                   # raises when there is no CUDA device at all
         _worker(0, 1, stage, args, 0, True)
         return 0
-    import torch.multiprocessing as mp
+    return _run_ranks(stage, args, world, prog)
+
+
+def _run_ranks(stage: int, args, world: int, prog: str) -> int:
+    """One worker per GPU without editing run.sh: this process becomes rank 0 and starts ranks 1..N-1 as plain
+    subprocesses of the same command line (environment RANK / WORLD_SIZE / LOCAL_RANK / MASTER_*), BEFORE it imports
+    torch itself, so the interpreters start, import and create their CUDA contexts side by side.  Only rank 0 writes
+    files (atomically, after the gather), so the all-or-nothing contract needs one rule: if any rank dies, everybody
+    dies before rank 0 reaches its write."""
+    import signal
+    import subprocess
+    import threading
     port = 29500 + os.getpid() % 2000
-    mp.spawn(_worker, args=(world, stage, args, port, True), nprocs=world, join=True)
-    return 0
+    tool = {"extract_embedding.py": "extract_embedding.py", "extract_speech_token.py": "extract_speech_token.py"}.get(prog, prog)
+    script = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", tool)
+    cmd = [sys.executable, script, "--dir", args.dir, "--onnx_path", args.onnx_path, "--num_thread", str(args.num_thread)]
+    base = dict(os.environ, WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), FY_CHILD_RANK="1")
+    kids = [subprocess.Popen(cmd, env=dict(base, RANK=str(r), LOCAL_RANK=str(r))) for r in range(1, world)]
+    done = threading.Event()
+
+    def watch():
+        while not done.is_set():
+            for k in kids:
+                rc = k.poll()
+                if rc not in (None, 0):
+                    sys.stderr.write(f"fangyan_b200: rank process {k.pid} exited with status {rc}; aborting, nothing written\n")
+                    for o in kids:
+                        if o.poll() is None:
+                            o.kill()
+                    os._exit(1)             # rank 0 may be blocked inside a collective: no exception can reach it
+            done.wait(0.2)
+
+    threading.Thread(target=watch, daemon=True).start()
+    os.environ.update(RANK="0", WORLD_SIZE=str(world), LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    try:
+        _worker(0, world, stage, args, port, False)
+    except BaseException:
+        done.set()
+        for k in kids:
+            if k.poll() is None:
+                k.send_signal(signal.SIGTERM)
+        raise
+    done.set()
+    rc = 0
+    for k in kids:
+        rc = rc or k.wait()
+    return 1 if rc else 0
 
 
 def main_embedding(argv=None) -> int:

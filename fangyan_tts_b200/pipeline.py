@@ -268,7 +268,10 @@ class Extractor:
         dev = self.eng.device
         dur = [u.samples.shape[0] / SR for u in utts]
         order, emb_p, tok_p, cnt_p = [], [], [], []
-        for idx in plan_batches(dur, self.max_batch_seconds, self.max_batch_utts):
+        batches = plan_batches(dur, self.max_batch_seconds, self.max_batch_utts)
+        if batches and len(batches[0]) > 2 * RAMP_UTTS:      # short ramp-up batch, as in extract()
+            batches[0:1] = [batches[0][:RAMP_UTTS], batches[0][RAMP_UTTS:]]
+        for idx in batches:
             lens = [utts[i].samples.shape[0] for i in idx]
             pcm = self.ring.upload([utts[i].samples[:, 0] for i in idx], int(sum(lens)))
             feat, frames = self.eng.fbank_cmn(pcm, lens)
