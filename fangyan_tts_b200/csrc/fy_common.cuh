@@ -121,6 +121,7 @@ struct Ctx {
   int* fb_mel_off = nullptr;       // [80] first fft bin
   int* fb_mel_len = nullptr;       // [80]
   int* fb_mel_ptr = nullptr;       // [80] offset into fb_mel_w
+  int fb_mel_nw = 0, wh_mel_nw = 0; // packed weights in fb_mel_w / wh_mel_w
   float2* fb_tw = nullptr;         // [256] twiddles for N=512
   float* wh_window = nullptr;      // [400] hann periodic
   float* wh_mel_w = nullptr;

@@ -6,6 +6,8 @@
 // imaginary lane) held in shared memory, Stockham autosort, radix 4/4/4/4/2 for 512 and 4/4/5/5 for 400.
 #include <math.h>
 
+#include <algorithm>
+
 #include <vector>
 
 #include "fy_common.cuh"
@@ -244,6 +246,8 @@ __global__ void fill_int_kernel(int* p, int n, int v) {
   if (i < n) p[i] = v;
 }
 
+#include "fy_fbank2.cuh"
+
 // Pass 1: log10(max(mel, 1e-10)) time-major into raw[total_frames, 128]; per-utterance max into umax keys.
 template <bool S16>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) logmel_kernel(const void* __restrict__ pcm,
@@ -458,7 +462,8 @@ int upload(Ctx* c, const std::vector<T>& h, T** d) {
   return FY_OK;
 }
 
-int upload_mel(Ctx* c, const std::vector<std::vector<float>>& bank, float** dw, int** doff, int** dlen, int** dptr) {
+int upload_mel(Ctx* c, const std::vector<std::vector<float>>& bank, float** dw, int** doff, int** dlen, int** dptr,
+               int* n_weights = nullptr) {
   std::vector<float> w;
   std::vector<int> off, len, ptr;
   for (const auto& row : bank) {
@@ -472,6 +477,7 @@ int upload_mel(Ctx* c, const std::vector<std::vector<float>>& bank, float** dw, 
     for (int k = first; k <= last; ++k) w.push_back(row[k]);
   }
   if (w.empty()) w.push_back(0.f);
+  if (n_weights) *n_weights = (int)w.size();
   FY_TRY(upload(c, w, dw));
   FY_TRY(upload(c, off, doff));
   FY_TRY(upload(c, len, dlen));
@@ -548,8 +554,14 @@ int frontend_init(Ctx* c) {
   FY_TRY(upload(c, hann, &c->wh_window));
   FY_TRY(upload(c, twiddles(512), &c->fb_tw));
   FY_TRY(upload(c, twiddles(400), &c->wh_tw));
-  FY_TRY(upload_mel(c, kaldi_bank(), &c->fb_mel_w, &c->fb_mel_off, &c->fb_mel_len, &c->fb_mel_ptr));
-  FY_TRY(upload_mel(c, slaney_bank(), &c->wh_mel_w, &c->wh_mel_off, &c->wh_mel_len, &c->wh_mel_ptr));
+  FY_TRY(upload_mel(c, kaldi_bank(), &c->fb_mel_w, &c->fb_mel_off, &c->fb_mel_len, &c->fb_mel_ptr, &c->fb_mel_nw));
+  FY_TRY(upload_mel(c, slaney_bank(), &c->wh_mel_w, &c->wh_mel_off, &c->wh_mel_len, &c->wh_mel_ptr, &c->wh_mel_nw));
+  FY_CHECK(c->fb_mel_nw <= fb2::kMelW, FY_ERR_STATE, "Kaldi mel bank has %d weights, the kernel holds %d", c->fb_mel_nw, fb2::kMelW);
+  FY_CUDA(cudaFuncSetAttribute(fb2::fbank2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(fb2::Smem)));
+  FY_CUDA(cudaFuncSetAttribute(fb2::fbank2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(fb2::Smem)));
+  FY_CHECK(c->wh_mel_nw <= lm2::kMelW, FY_ERR_STATE, "Slaney mel bank has %d weights, the kernel holds %d", c->wh_mel_nw, lm2::kMelW);
+  FY_CUDA(cudaFuncSetAttribute(lm2::logmel2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(lm2::Smem)));
+  FY_CUDA(cudaFuncSetAttribute(lm2::logmel2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(lm2::Smem)));
   // matcha 24 kHz mel (row N4): periodic Hann(1920), 1920-point twiddles, librosa mel(sr 24000, n_fft 1920, 80)
   std::vector<float> hann24(kMmN);
   for (int i = 0; i < kMmN; ++i) hann24[i] = (float)(0.5 - 0.5 * cos(2.0 * M_PI * i / (double)kMmN));
@@ -560,21 +572,41 @@ int frontend_init(Ctx* c) {
 }
 
 // launchers used by the pipeline code as well as the C ABI ------------------------------------------------
+int fbank2_slots(int n_utts, int total_frames) { return ((total_frames + 15 * n_utts) >> 4) + 1; }
+
 int launch_fbank(Ctx* c, const void* pcm, int dtype, const int* pcm_off, const int* frame_off, int n_utts,
-                 int total_frames, float* feat) {
+                 int total_frames, float* feat, void* ws) {
   if (total_frames <= 0) return FY_OK;
   MelTable mt{c->fb_mel_w, c->fb_mel_off, c->fb_mel_len, c->fb_mel_ptr};
-  const int pairs = ((total_frames + n_utts) >> 1) + 1;   // utterance-local pair slots (see find_slot_utt)
-  const int grid = (pairs + kWarpsPerBlock - 1) / kWarpsPerBlock;
+  static const bool v1 = [] { const char* e = getenv("FY_FRONTEND_V1"); return e && e[0] == '1'; }();
+  if (v1) {
+    const int pairs = ((total_frames + n_utts) >> 1) + 1;   // utterance-local pair slots (see find_slot_utt)
+    const int grid = (pairs + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    if (dtype == FY_PCM_S16)
+      fbank_kernel<true><<<grid, kWarpsPerBlock * 32, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,
+                                                                     c->fb_window, c->fb_tw, mt, feat);
+    else
+      fbank_kernel<false><<<grid, kWarpsPerBlock * 32, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,
+                                                                      c->fb_window, c->fb_tw, mt, feat);
+    FY_CUDA(cudaGetLastError());
+    cmn_kernel<<<n_utts, 320, 0, c->stream>>>(feat, frame_off);
+    c->launches += 2;
+    FY_CUDA(cudaGetLastError());
+    return FY_OK;
+  }
+  const int slots = fbank2_slots(n_utts, total_frames);
+  float* psum = reinterpret_cast<float*>(ws);                 // [slots][80] per-CTA column sums, then [n_utts][80] means
+  float* mean = psum + (size_t)slots * 80;
+  const int grid = std::min(slots, 3 * c->num_sms);            // persistent: three CTAs per SM walk the slots
   if (dtype == FY_PCM_S16)
-    fbank_kernel<true><<<grid, kWarpsPerBlock * 32, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,
-                                                                   c->fb_window, c->fb_tw, mt, feat);
+    fb2::fbank2_kernel<true><<<grid, fb2::kThreads, sizeof(fb2::Smem), c->stream>>>(pcm, pcm_off, frame_off, n_utts, slots,
+                                                                                    c->fb_window, c->fb_tw, mt, c->fb_mel_nw, feat, psum);
   else
-    fbank_kernel<false><<<grid, kWarpsPerBlock * 32, 0, c->stream>>>(pcm, pcm_off, frame_off, n_utts, total_frames,
-                                                                    c->fb_window, c->fb_tw, mt, feat);
-  FY_CUDA(cudaGetLastError());
-  cmn_kernel<<<n_utts, 320, 0, c->stream>>>(feat, frame_off);
-  c->launches += 2;
+    fb2::fbank2_kernel<false><<<grid, fb2::kThreads, sizeof(fb2::Smem), c->stream>>>(pcm, pcm_off, frame_off, n_utts, slots,
+                                                                                     c->fb_window, c->fb_tw, mt, c->fb_mel_nw, feat, psum);
+  fb2::cmn_mean_kernel<<<n_utts, 96, 0, c->stream>>>(psum, frame_off, mean);
+  fb2::cmn_sub_kernel<<<slots, fb2::kThreads, 0, c->stream>>>(feat, frame_off, n_utts, mean);
+  c->launches += 3;
   FY_CUDA(cudaGetLastError());
   return FY_OK;
 }
@@ -604,17 +636,18 @@ using namespace fy;
 extern "C" {
 
 size_t fy_fbank_workspace_bytes(int n_utts, int total_frames) {
-  (void)n_utts; (void)total_frames;
-  return 256;
+  if (n_utts <= 0 || total_frames < 0) return 256;
+  return ((size_t)fbank2_slots(n_utts, total_frames) + (size_t)n_utts) * 80 * sizeof(float) + 256;
 }
 
 int fy_fbank_cmn(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
                  int n_utts, int total_frames, float* feat, void* ws, size_t ws_bytes) {
-  (void)ws; (void)ws_bytes;
-  FY_CHECK(ctx && pcm && pcm_off && frame_off && feat, FY_ERR_ARG, "fy_fbank_cmn: NULL argument");
+  FY_CHECK(ctx && pcm && pcm_off && frame_off && feat && ws, FY_ERR_ARG, "fy_fbank_cmn: NULL argument");
+  FY_CHECK(ws_bytes >= fy_fbank_workspace_bytes(n_utts, total_frames), FY_ERR_NOMEM, "fy_fbank_cmn: workspace too small");
+  FY_CHECK((reinterpret_cast<uintptr_t>(ws) & 15) == 0, FY_ERR_ARG, "fy_fbank_cmn: workspace must be 16-byte aligned");
   FY_CHECK(n_utts > 0 && total_frames >= 0, FY_ERR_ARG, "fy_fbank_cmn: bad sizes");
   FY_CHECK(pcm_dtype == FY_PCM_S16 || pcm_dtype == FY_PCM_F32, FY_ERR_ARG, "fy_fbank_cmn: bad pcm dtype");
-  return launch_fbank(reinterpret_cast<Ctx*>(ctx), pcm, pcm_dtype, pcm_off, frame_off, n_utts, total_frames, feat);
+  return launch_fbank(reinterpret_cast<Ctx*>(ctx), pcm, pcm_dtype, pcm_off, frame_off, n_utts, total_frames, feat, ws);
 }
 
 size_t fy_logmel_workspace_bytes(int n_utts, int total_frames) {
@@ -632,6 +665,26 @@ int fy_logmel(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_of
   Ctx* c = reinterpret_cast<Ctx*>(ctx);
   float* raw = reinterpret_cast<float*>(ws);
   int* umax = reinterpret_cast<int*>(raw + (size_t)total_frames * 128);
+  // The second-generation log-mel kernel (lm2, FY_LOGMEL_V2=1) is parity-green but measured SLOWER than the first
+  // (2.47 against 2.11 ms at 1,024 x 10 s): with the same shared-memory 400-point transform its CTA-wide staging and
+  // barriers cost more than they save, so the first generation stays the default here.
+  static const bool v2 = [] { const char* e = getenv("FY_LOGMEL_V2"); return e && e[0] == '1'; }();
+  if (v2) {
+    MelTable mt{c->wh_mel_w, c->wh_mel_off, c->wh_mel_len, c->wh_mel_ptr};
+    const int slots = fbank2_slots(n_utts, total_frames);
+    fill_int_kernel<<<(n_utts + 255) / 256, 256, 0, c->stream>>>(umax, n_utts, (int)0x80000000);
+    const int grid = std::min(slots, 3 * c->num_sms);          // persistent: three CTAs per SM walk the slots
+    if (pcm_dtype == FY_PCM_S16)
+      lm2::logmel2_kernel<true><<<grid, lm2::kThreads, sizeof(lm2::Smem), c->stream>>>(pcm, pcm_off, frame_off, n_utts, slots,
+                                                                                       c->wh_window, c->wh_tw, mt, c->wh_mel_nw, mel, umax);
+    else
+      lm2::logmel2_kernel<false><<<grid, lm2::kThreads, sizeof(lm2::Smem), c->stream>>>(pcm, pcm_off, frame_off, n_utts, slots,
+                                                                                        c->wh_window, c->wh_tw, mt, c->wh_mel_nw, mel, umax);
+    lm2::logmel2_finish_kernel<<<slots, lm2::kThreads, 0, c->stream>>>(mel, frame_off, n_utts, umax);
+    c->launches += 3;
+    FY_CUDA(cudaGetLastError());
+    return FY_OK;
+  }
   FY_TRY(launch_logmel_raw(c, pcm, pcm_dtype, pcm_off, frame_off, n_utts, total_frames, raw, umax));
   dim3 grid((max_frames + 31) / 32, n_utts);
   logmel_finish_kernel<<<grid, 256, 0, c->stream>>>(raw, frame_off, umax, mel);
