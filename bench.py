@@ -301,6 +301,25 @@ def frontend_figures(eng, hbm, batch=1024):
         gbs = bps * secs / (ms * 1e-3) / 1e9
         out[name] = {"ms": ms, "alg_bytes_per_audio_s": bps, "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / hbm,
                      "audio_hours_per_s": secs / 3600.0 / (ms * 1e-3)}
+    # row A2: 24 kHz -> 16 kHz polyphase resampler on the same number of 10 s clips (fp32 in, fp32 out: 160,000 B/audio-s)
+    x24 = torch.randn(batch * 240000, device="cuda") * 0.1
+    l24 = [240000] * batch
+    for _ in range(3):
+        eng.resample(x24, l24, 24000, 16000)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(5):
+        eng.resample(x24, l24, 24000, 16000)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 5
+    gbs = 160000.0 * secs / (ms * 1e-3) / 1e9
+    out["resample_24k_16k"] = {"ms": ms, "alg_bytes_per_audio_s": 160000.0, "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / hbm,
+                               "audio_hours_per_s": secs / 3600.0 / (ms * 1e-3), "l2": "1 GB in + 0.66 GB out per call"}
+    out["bound_note"] = ("fbank / log-mel are fp32-issue bound, not HBM bound: one 512-point real FFT + window + mel + log is ~1.1 M "
+                         "instructions per audio-second against 64 KB, so 30 % of the HBM peak would need ~94 % of the SM's fp32 "
+                         "issue rate; see DESIGN.md section 4.4")
     return out
 
 

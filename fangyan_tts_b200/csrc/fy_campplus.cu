@@ -24,7 +24,10 @@
 namespace fy {
 namespace {
 
-struct BN { float* scale = nullptr; float* shift = nullptr; };
+struct BN {
+  float* scale = nullptr; float* shift = nullptr;
+  __half *scale_h = nullptr, *shift_h = nullptr;   // fp16 copies padded with zeros to a multiple of 64 (+64): GEMM A-side transform
+};
 
 struct ConvW {           // a 32->32 FCM convolution as a GEMM B operand [32, blocks * 64] fp16 (two taps per K block)
   __half* w = nullptr;
@@ -101,6 +104,12 @@ int load_bn(const Loader& L, const std::string& pre, int C, bool affine, BN* bn)
   }
   FY_TRY(dev_upload(L.p, sc, &bn->scale));
   FY_TRY(dev_upload(L.p, sh, &bn->shift));
+  const size_t padded = ((size_t)C + 63) / 64 * 64 + 64;
+  std::vector<float> scp(padded, 0.f), shp(padded, 0.f);
+  std::copy(sc.begin(), sc.end(), scp.begin());
+  std::copy(sh.begin(), sh.end(), shp.begin());
+  FY_TRY(upload_f16(L.p, scp, &bn->scale_h));
+  FY_TRY(upload_f16(L.p, shp, &bn->shift_h));
   return FY_OK;
 }
 
@@ -362,6 +371,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   }
   static const bool gate_env = [] { const char* e = getenv("FY_CAM_FUSED_GATE"); return !(e && e[0] == '0'); }();
   const bool fused_gate = gate_env && max_seg <= camk::kGateMaxSeg;
+  static const bool fused_bn = [] { const char* e = getenv("FY_CAM_FUSED_BN"); return !(e && e[0] == '0'); }();
   Layout lay = make_layout(p, n_utts, row, nseg);
   FY_CHECK(lay.total <= ws_bytes, FY_ERR_NOMEM, "fy_campplus_forward: workspace %zu < %zu bytes", ws_bytes, lay.total);
   const int R50 = lay.R50, R100 = lay.R100;
@@ -450,13 +460,19 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
     const int dil = cf.dilation[b];
     for (int l = 0; l < cf.layers[b]; ++l) {
       const DenseW& d = p->blocks[b][l];
-      {
+      if (!fused_bn) {
         const size_t n = (size_t)R50 * (d.cin / 8);
         camk::bnrelu_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(cat, ld, R50, d.cin, d.bn1.scale, d.bn1.shift, hin, 1024);
+        c->launches += 1;
       }
       {
         GemmArgs g;
-        FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, d.cin, 1024, 128));
+        if (fused_bn) {   // BN1 + ReLU of the concat buffer applied to the A tiles inside the GEMM (GemmArgs::a_scale)
+          FY_TRY(make_tmap_bf16(&g.tmap_a, cat, R50, d.cin, ld, 128));
+          g.a_scale = d.bn1.scale_h; g.a_shift = d.bn1.shift_h;
+        } else {
+          FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, d.cin, 1024, 128));
+        }
         g.tmap_b = d.m1; g.M = R50; g.N = 128; g.op = OP_F16;
         g.seg[g.nseg++] = GemmSeg{0, 0, 0, (d.cin + 63) / 64};
         g.epi.mode = EPI_BF16; g.epi.out_f16 = 1; g.epi.act = ACT_RELU; g.epi.out = hb; g.epi.ldo = 128;
@@ -464,10 +480,10 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
         FY_TRY(run_gemm(c, g, 2.0 * vT2 * 128 * d.cin));
       }
       if (fused_gate) {
-        c->launches += 2;  // bnrelu, cam_ctx_gate
+        c->launches += 1;  // cam_ctx_gate
         camk::cam_ctx_gate_kernel<<<n_utts, 256, 0, st>>>(hb, d_B, d_T2, d_segbase, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
       } else {
-        c->launches += 3;  // bnrelu, cam_segsum, cam_gate
+        c->launches += 2;  // cam_segsum, cam_gate
         camk::cam_segsum_kernel<<<nseg, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, d_segutt, cf.seg_len, segsum);
         camk::cam_gate_kernel<<<nseg, 128, 0, st>>>(segsum, d_T2, d_segbase, d_segutt, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
       }
@@ -482,10 +498,16 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
     }
     const TransW& tr = p->trans[b];
     {
-      const size_t n = (size_t)R50 * (tr.cin / 8);
-      camk::bnrelu_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(cat, ld, R50, tr.cin, tr.bn.scale, tr.bn.shift, hin, 1024);
       GemmArgs g;
-      FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, tr.cin, 1024, 128));
+      if (fused_bn) {
+        FY_TRY(make_tmap_bf16(&g.tmap_a, cat, R50, tr.cin, ld, 128));
+        g.a_scale = tr.bn.scale_h; g.a_shift = tr.bn.shift_h;
+      } else {
+        const size_t n = (size_t)R50 * (tr.cin / 8);
+        camk::bnrelu_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(cat, ld, R50, tr.cin, tr.bn.scale, tr.bn.shift, hin, 1024);
+        c->launches += 1;
+        FY_TRY(make_tmap_bf16(&g.tmap_a, hin, R50, tr.cin, 1024, 128));
+      }
       g.tmap_b = tr.m; g.M = R50; g.N = tr.cout; g.op = OP_F16;
       g.seg[g.nseg++] = GemmSeg{0, 0, 0, (tr.cin + 63) / 64};
       g.epi.mode = EPI_BF16; g.epi.out_f16 = 1; g.epi.out = H(lay.o_cat[b + 1]); g.epi.ldo = ctot[b + 1];
@@ -496,7 +518,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
   // ---- BN + ReLU -> statistics pooling -> dense -> BN
   const int C = ctot[cf.n_blocks];
   float* stats = Fp(lay.o_stats);
-  c->launches += 12;  // memset, 5 masks, stem, 3 transit bnrelu, stats, dense
+  c->launches += 9;   // memset, 5 masks, stem, stats, dense
   camk::stats_kernel<<<n_utts, 512, 0, st>>>(H(lay.o_cat[cf.n_blocks]), C, C, d_B, d_T2, p->out_bn.scale, p->out_bn.shift, stats);
   camk::dense_kernel<<<n_utts, 256, 2 * C * 4, st>>>(stats, 2 * C, cf.embed_dim, p->dense_w, p->dense_bn.scale,
                                                      p->dense_bn.shift, emb);

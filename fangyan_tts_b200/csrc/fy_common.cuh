@@ -95,6 +95,12 @@ struct GemmArgs {
   int nseg = 0;
   GemmSeg seg[kMaxSeg];
   GemmEpi epi;
+  // Optional A-side transform (fp16 operands, single-CTA kernels, no fused segments): every A tile is rewritten in shared
+  // memory as relu(a * a_scale[k] + a_shift[k]) (k = the tile's A column) between its TMA arrival and its MMA, by the two
+  // otherwise idle control warps.  This is how CAMPPlus folds BatchNorm + ReLU of the growing concat buffer into the
+  // bottleneck / transit GEMMs instead of a separate pass over the buffer.  Tables: fp16, padded to a multiple of 64.
+  const __half* a_scale = nullptr;
+  const __half* a_shift = nullptr;
 };
 
 // Encode a 2-D bf16 row-major [rows, cols] tensor map (ld in elements) with a {64, box_rows} box, 128B swizzle.

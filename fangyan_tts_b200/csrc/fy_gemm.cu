@@ -135,7 +135,10 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tfull_bar = empty_bar + C::kStages;
   uint64_t* tempty_bar = tfull_bar + C::kAccStages;
-  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + C::kAccStages);
+  uint64_t* xf_bar = tempty_bar + C::kAccStages;          // [kStages] A tile transformed (GemmArgs::a_scale), 2 arrivals
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(xf_bar + C::kStages);
+  static_assert((3 * C::kStages + 2 * C::kAccStages) * 8 + 8 <= 256, "barrier block");
+  const bool xform = !PAIR && OP == OP_F16 && args.a_scale != nullptr;
   float* s_scale = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);
   float* s_bias = s_scale + BN;
 
@@ -164,6 +167,7 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
     for (int i = 0; i < C::kStages; ++i) {
       ptx::mbar_init(&full_bar[i], 1);
       ptx::mbar_init(&empty_bar[i], 1);
+      ptx::mbar_init(&xf_bar[i], 2);
     }
     for (int i = 0; i < C::kAccStages; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
@@ -276,7 +280,7 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
           }
           for (int kb = 0; kb < nkb; ++kb) {
             FY_SP(const long long sp_b = clock64();)
-            ptx::mbar_wait(&full_bar[stage], phase);
+            ptx::mbar_wait(xform ? &xf_bar[stage] : &full_bar[stage], phase);   // transformed tiles imply landed tiles
             FY_SP(sp_wf += clock64() - sp_b;)
             ptx::tc_fence_after();
             const uint32_t a_addr = ptx::smem_u32(tiles + stage * C::kStageBytes);
@@ -301,6 +305,47 @@ __global__ void __launch_bounds__(cta_threads<BN>(), Cfg<BN, NCTA>::kCtasPerSm) 
       FY_SP(if (lane == 0) { atomicAdd(&g_stall[sp_slot + 2], (unsigned long long)sp_wf);
                              atomicAdd(&g_stall[sp_slot + 3], (unsigned long long)sp_we);
                              atomicAdd(&g_stall[sp_slot + 4], (unsigned long long)(clock64() - sp_t0)); })
+    }
+  } else if (warp < 4) {
+    // ===================== A-tile transform (warps 2 and 3, only when GemmArgs::a_scale is set) =====================
+    // The tile is [128 rows][128 bytes] with the 128-byte swizzle: the 16-byte chunk at position c' of row r holds the
+    // logical chunk c' ^ (r & 7), i.e. A columns 8 (c' ^ (r & 7)) .. + 7 of the K block.  Thread t takes position t & 7
+    // of the rows (t >> 3) + 8 i: its logical chunk -- and so its eight scale / shift pairs -- is the same for all
+    // sixteen rows, loaded once per K block.
+    if (xform) {
+      const int t = threadIdx.x - 64;
+      const int cpos = t & 7, r0 = t >> 3;
+      const int clog = cpos ^ (r0 & 7);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = worker; tile < num_tiles; tile += n_workers) {
+        for (int s = 0; s < args.nseg; ++s) {
+          const GemmSeg sg = args.seg[s];
+          for (int kb = 0; kb < sg.nkb; ++kb) {
+            const int k0 = sg.a_col + kb * BKE + clog * 8;
+            const uint4 sc4 = __ldg(reinterpret_cast<const uint4*>(args.a_scale + k0));
+            const uint4 sh4 = __ldg(reinterpret_cast<const uint4*>(args.a_shift + k0));
+            const __half2* sc = reinterpret_cast<const __half2*>(&sc4);
+            const __half2* sh = reinterpret_cast<const __half2*>(&sh4);
+            const __half2 zero = __float2half2_rn(0.f);
+            ptx::mbar_wait(&full_bar[stage], phase);
+            uint8_t* a_tile = tiles + stage * C::kStageBytes + cpos * 16;
+#pragma unroll 4
+            for (int i = 0; i < 16; ++i) {
+              uint4* p = reinterpret_cast<uint4*>(a_tile + (r0 + 8 * i) * 128);
+              uint4 v = *p;
+              __half2* h = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) h[j] = __hmax2(__hfma2(h[j], sc[j], sh[j]), zero);
+              *p = v;
+            }
+            asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");   // generic-proxy writes -> the MMA's async reads
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&xf_bar[stage]);
+            if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
     }
   } else if (warp >= 4) {
     // ===================== epilogue (warp w drains TMEM lane quarter w % 4; warps 8..11 take the upper columns) ====
