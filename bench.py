@@ -526,11 +526,11 @@ def run_ours(args):
         "roofline": {"bound": "tensor", "kernel": "gemm_kernel<BN, OP, NCTA> (tcgen05; all launches: S3 encoder "
                                                   "bf16x3 CTA-pair tiles + CAMPPlus fp16 tiles)",
                      "achieved": achieved, "peak": tf_sust, "unit": "TFLOP/s", "frac": achieved / tf_sust,
-                     "traffic": None,
-                     "traffic_profiled_elsewhere": {"bytes_per_launch": 4.11e8, "rows": 16400,
-                                                    "source": "profiles/r01_ncu_gemm_pair_bf16x3.md (ncu --set full, mean of "
-                                                              "the four S3 layer GEMMs at 16.4 k rows; this run's batches "
-                                                              "are ~3.7x larger and were not captured)"},
+                     # dram__bytes_read + write per launch, ncu --set full at THIS batch size (2,400 audio-s per batch):
+                     # mean of the four S3 layer GEMMs, > 96 % of the FLOPs counted in `achieved`
+                     "traffic": 1.755e9 if args.batch_seconds == 2400.0 and args.precision == "bf16x3" else None,
+                     "traffic_source": "profiles/r02_ncu_gemm_pair_bench.md (ncu --set full of QKV / O / fc1 / fc2 at 370 "
+                                       "bench utterances = one 2,400 audio-s batch: 1.34 / 0.92 / 1.79 / 2.97 GB per launch)",
                      "peak_source": f"{which} sustained cuBLAS bf16",
                      "executed_tflops": achieved * x3, "executed_frac": achieved * x3 / tf_sust,
                      "note": "achieved counts each MAC once; split-bf16 executes three tensor-core products per MAC "
