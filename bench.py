@@ -335,15 +335,31 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    t_start = time.perf_counter()
+    watchdog = float(os.environ.get("FY_BENCH_WATCHDOG", "240"))
+
+    def mark(stage):
+        """One stderr line per phase and rank, and a watchdog: a phase that takes longer than FY_BENCH_WATCHDOG
+        seconds dumps every thread's stack and ends the process (a hung rank must not hold an 8-GPU box)."""
+        import faulthandler
+        sys.stderr.write(f"[bench r{rank}/{world} +{time.perf_counter() - t_start:6.1f}s] {stage}\n")
+        sys.stderr.flush()
+        faulthandler.cancel_dump_traceback_later()
+        if watchdog > 0 and stage != "done":
+            faulthandler.dump_traceback_later(watchdog, exit=True)
+
+    mark("start")
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mark("process group up")
     eng = Engine(local, args.precision)
     cam_cfg, s3_cfg = CamPlusConfig(), S3Config()
     cam_state, s3_state = synth_weights.campplus_state(cam_cfg), synth_weights.s3tok_state(s3_cfg)
     eng.load_campplus(cam_state, cam_cfg)                                # random-init weights of the named architectures
     eng.load_s3tok(s3_state, s3_cfg)
 
+    mark("weights on the device")
     # ---- the job: one utterance list, identical on every rank, sharded by duration like the CLIs shard wav.scp
     n_total = world * args.utts
     utts = workload(n_total, 1986 + 2)
@@ -426,8 +442,14 @@ def run_ours(args):
         return max_over_ranks(a.elapsed_time(b))
 
     warm = max(args.warmup, 3)
-    for _ in range(warm):
+    mark("shard resident")
+    for k in range(warm):
         step_device()
+        if k == 0:
+            torch.cuda.synchronize()
+            mark("first step (with the first exchange) done")
+    torch.cuda.synchronize()
+    mark("warm-up done")
     # ---- the exchange delivered exactly what the ranks computed (fingerprints of index x row bits, all-reduced)
     fp = torch.stack([D.checksum(gidx, last["emb"]), D.checksum_ragged(gidx, gcnt, last["tok"])])
     if world > 1:
@@ -447,6 +469,7 @@ def run_ours(args):
         clocks.start()
     ms = timed(step_device, args.steps)
     clk = clocks.stop() if rank == 0 else None
+    mark("timed steps done")
     eng.lib.fy_profile_read(eng.h, prof, 10)
     eng.lib.fy_profile_enable(eng.h, 0)
     p = list(prof)
@@ -464,7 +487,9 @@ def run_ours(args):
                           "rank 0 + all_reduce payload", "verified": gather_ok,
                   "share_of_step": g_ms / (ms / args.steps)}
 
+    mark("exchange timed")
     step_e2e()                                            # warm the pinned buffers
+    mark("first e2e step done")
     e2e_steps = max(1, min(args.steps, 3))
     barrier()
     t0 = time.perf_counter()
@@ -472,6 +497,7 @@ def run_ours(args):
         step_e2e()
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
+    mark("e2e timed")
 
     hbm, tf_burst, tf_sust, which = peaks()
     fe = None
@@ -494,10 +520,14 @@ def run_ours(args):
                              "reported for BASELINE configs[3] only"}
     del cam_state, s3_state
 
+    # Every GPU number is in hand: leave the process group NOW, so that the other ranks exit instead of spinning in a
+    # barrier next to rank 0's CPU leg (oracle for `parity`).
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    mark("process group closed")
     if rank != 0:
-        if world > 1:
-            dist.barrier()                                 # rank 0 is still running the CPU oracle for `parity`
-            dist.destroy_process_group()
+        mark("done")
         return 0
     ms_per_step = ms / args.steps
     value = audio_s / 3600.0 / (ms_per_step / 1e3)
@@ -564,9 +594,7 @@ def run_ours(args):
         if not line["parity"]["pass"]:
             rc = 3
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    mark("done")
     if gather_ok is False:
         sys.stderr.write("bench: the gathered results do not match the per-rank fingerprints\n")
         rc = 4
