@@ -47,6 +47,7 @@ PROTOTYPES = {
     "fy_resample": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I]),
     "fy_fbank_workspace_bytes": (_Z, [_I, _I]),
     "fy_fbank_cmn": (_I, [_P, _P, _I, _P, _P, _I, _I, _P, _P, _Z]),
+    "fy_fbank_cmn_static": (_I, [_P, _P, _I, _P, _P, _I, _I, _P]),
     "fy_logmel_workspace_bytes": (_Z, [_I, _I]),
     "fy_logmel": (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _P, _P, _Z]),
     "fy_matcha_mel": (_I, [_P, _P, _I, _P, _P, _I, _I, _P]),

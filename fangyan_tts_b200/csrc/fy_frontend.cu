@@ -10,7 +10,15 @@
 
 #include <vector>
 
+#include <mutex>
+
 #include "fy_common.cuh"
+
+// Scratch of fy_fbank_cmn_static (the entry point that allocates nothing, end of this file): per-CTA column sums and
+// per-utterance means of the second-generation fbank.  Resident on every GPU that loads the library until the process
+// exits.  In HOST code this name is only a stand-in for the symbol: kernels get the device address that
+// fbank_static_setup() asks the runtime for (cudaGetSymbolAddress), once per device.
+static __device__ __align__(256) unsigned char g_fbank_static_ws[FY_FBANK_STATIC_WS_BYTES];
 
 namespace fy {
 namespace {
@@ -541,6 +549,28 @@ std::vector<std::vector<float>> slaney_bank(int nm = 128, int nfft = 400, double
 
 }  // namespace
 
+// Device address of g_fbank_static_ws on each device that has a context.  Runs inside fy_create (frontend_init) with
+// `device` current, so the hot call below never asks the runtime for anything.
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_fbank_static_ptr[kMaxDevices] = {};
+std::mutex g_fbank_static_mu;
+}  // namespace
+
+int fbank_static_setup(int device) {
+  FY_CHECK(device >= 0 && device < kMaxDevices, FY_ERR_ARG, "device ordinal %d outside [0, %d)", device, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_fbank_static_mu);
+  if (g_fbank_static_ptr[device]) return FY_OK;
+  int cur = -1;
+  FY_CUDA(cudaGetDevice(&cur));
+  FY_CHECK(cur == device, FY_ERR_STATE, "fbank_static_setup: device %d is current, not %d", cur, device);
+  void* p = nullptr;
+  FY_CUDA(cudaGetSymbolAddress(&p, g_fbank_static_ws));
+  FY_CHECK(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0, FY_ERR_STATE, "static fbank scratch has no aligned device address");
+  g_fbank_static_ptr[device] = p;
+  return FY_OK;
+}
+
 int frontend_init(Ctx* c) {
   // Povey window = hann(400, periodic=False)^0.85 in fp32 (kaldi.py:98-100)
   std::vector<float> povey(400), hann(400);
@@ -568,6 +598,7 @@ int frontend_init(Ctx* c) {
   FY_TRY(upload(c, hann24, &c->mm_window));
   FY_TRY(upload(c, twiddles(kMmN), &c->mm_tw));
   FY_TRY(upload_mel(c, slaney_bank(kMmMels, kMmN, 24000.0), &c->mm_mel_w, &c->mm_mel_off, &c->mm_mel_len, &c->mm_mel_ptr));
+  FY_TRY(fbank_static_setup(c->device));
   return FY_OK;
 }
 
@@ -648,6 +679,27 @@ int fy_fbank_cmn(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm
   FY_CHECK(n_utts > 0 && total_frames >= 0, FY_ERR_ARG, "fy_fbank_cmn: bad sizes");
   FY_CHECK(pcm_dtype == FY_PCM_S16 || pcm_dtype == FY_PCM_F32, FY_ERR_ARG, "fy_fbank_cmn: bad pcm dtype");
   return launch_fbank(reinterpret_cast<Ctx*>(ctx), pcm, pcm_dtype, pcm_off, frame_off, n_utts, total_frames, feat, ws);
+}
+
+// fy_fbank_cmn for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc):
+// same kernels, same launch order, the scratch is g_fbank_static_ws instead of a caller workspace.  No cudaMalloc /
+// cudaFree / allocating library call on this path; three launches on the context's stream.  Nothing has to be cleared
+// between calls: every scratch element a call reads (slot sums, utterance means) is written earlier in the same call.
+// All calls on a device share the array, so two calls that overlap on the GPU (different streams or contexts) race.
+int fy_fbank_cmn_static(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
+                        int n_utts, int total_frames, float* feat) {
+  FY_CHECK(ctx && pcm && pcm_off && frame_off && feat, FY_ERR_ARG, "fy_fbank_cmn_static: NULL argument");
+  FY_CHECK(n_utts > 0 && total_frames >= 0, FY_ERR_ARG, "fy_fbank_cmn_static: bad sizes");
+  FY_CHECK(pcm_dtype == FY_PCM_S16 || pcm_dtype == FY_PCM_F32, FY_ERR_ARG, "fy_fbank_cmn_static: bad pcm dtype");
+  const size_t need = fy_fbank_workspace_bytes(n_utts, total_frames);
+  FY_CHECK(need <= (size_t)FY_FBANK_STATIC_WS_BYTES, FY_ERR_NOMEM,
+           "fy_fbank_cmn_static: %d utterances / %d frames need %zu bytes of scratch, the static array holds %zu "
+           "(total_frames / 16 + 2 n_utts + 1 <= %zu rows); use fy_fbank_cmn with a caller workspace",
+           n_utts, total_frames, need, (size_t)FY_FBANK_STATIC_WS_BYTES, ((size_t)FY_FBANK_STATIC_WS_BYTES - 256) / 320);
+  Ctx* c = reinterpret_cast<Ctx*>(ctx);
+  void* ws = (c->device >= 0 && c->device < kMaxDevices) ? g_fbank_static_ptr[c->device] : nullptr;
+  FY_CHECK(ws != nullptr, FY_ERR_STATE, "fy_fbank_cmn_static: no scratch address for device %d (fy_create sets it up)", c->device);
+  return launch_fbank(c, pcm, pcm_dtype, pcm_off, frame_off, n_utts, total_frames, feat, ws);
 }
 
 size_t fy_logmel_workspace_bytes(int n_utts, int total_frames) {

@@ -130,6 +130,23 @@ size_t fy_fbank_workspace_bytes(int n_utts, int total_frames);
 int fy_fbank_cmn(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
                  int n_utts, int total_frames, float* feat, void* ws, size_t ws_bytes);
 
+/* ---- fy_fbank_cmn without any allocation ------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments,
+ * kernels and results as fy_fbank_cmn, minus the workspace: the scratch (per-CTA column sums + per-utterance means)
+ * is a static __device__ array of FY_FBANK_STATIC_WS_BYTES inside the library, resident on every GPU that loads
+ * it until the process exits; fy_create looks its device address up once per device.  The call makes no cudaMalloc /
+ * cudaFree / allocating library call and launches three kernels on the context's stream.
+ * Limit: fy_fbank_workspace_bytes(n_utts, total_frames) <= FY_FBANK_STATIC_WS_BYTES, i.e.
+ * total_frames / 16 + 2 n_utts + 1 <= 13,106 rows (64 utterances of 30 s, or one prompt of any length the path
+ * takes); beyond it the call fails with FY_ERR_NOMEM and a message naming both sizes -- use fy_fbank_cmn then.
+ * All calls on one GPU share the array and it keeps the previous call's contents (nothing needs clearing: a call
+ * writes every element before it reads it), so calls that OVERLAP on the GPU -- two streams, two contexts -- race;
+ * serialise them or give the concurrent one a workspace through fy_fbank_cmn. */
+#define FY_FBANK_STATIC_WS_BYTES (4u << 20)
+int fy_fbank_cmn_static(fy_ctx* ctx, const void* pcm, int pcm_dtype, const int32_t* pcm_off, const int32_t* frame_off,
+                        int n_utts, int total_frames, float* feat);
+
 /* ---- A5: whisper.log_mel_spectrogram(audio, n_mels=128) ---------------------------------------------------
  * tools/extract_speech_token.py:38, cosyvoice/cli/frontend.py:98.
  * mel: packed; utterance b occupies 128 * T_b floats starting at 128 * frame_off[b], laid out [128][T_b] exactly
