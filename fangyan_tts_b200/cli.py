@@ -106,6 +106,18 @@ def _n_gpus() -> int:
     return max(1, min(n, want))
 
 
+def _seconds_since_exec() -> float:
+    """Seconds since this process was created (interpreter start, imports ...), from /proc; 0.0 when unknown."""
+    try:
+        with open("/proc/self/stat") as f:
+            start_ticks = int(f.read().rsplit(")", 1)[1].split()[19])
+        with open("/proc/uptime") as f:
+            up = float(f.read().split()[0])
+        return max(0.0, up - start_ticks / os.sysconf("SC_CLK_TCK"))
+    except (OSError, ValueError, IndexError):
+        return 0.0
+
+
 def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: bool):
     import torch
     from . import distributed as D
@@ -117,16 +129,22 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
 
     env = _dist_env()
     rank = env[0] if env and not spawned else local_rank
+    t_entry = time.perf_counter()
+    since_exec = _seconds_since_exec()                     # interpreter start + imports, for the time split
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", str(port))
+        # the job's only traffic is a few point-to-point sends and two tiny all_reduces: no NVLink-SHARP set-up
+        os.environ.setdefault("NCCL_NVLS_ENABLE", "0")
         torch.cuda.set_device(local_rank)
-        D.init(rank, world, "nccl", port, torch.device("cuda", local_rank))
+        # no device_id: the communicator is NOT built here (8 ranks: ~10 s) but by the first collective, below
+        D.init(rank, world, "nccl", port, None)
     t_start = time.perf_counter()
+    t_init = t_start - t_entry
     warm = None
     if world > 1:
-        # NCCL builds its communicator at the first collective (~1.5 s): do that under the weight upload and the header
-        # scan instead of in front of the result gather
+        # NCCL builds its communicator at the first collective (1.5 s at 2 ranks, ~10 s at 8): a side thread does that
+        # under the weight upload, the header scan AND the extraction loop; it is joined in front of the result gather
         import threading
 
         def _warm():
@@ -214,8 +232,6 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
     def to_dev(values, dtype):
         return torch.from_numpy(np.asarray(values, dtype=dtype)).to(dev, non_blocking=True)
 
-    if warm is not None:
-        warm.join()
     t_loop = time.perf_counter()
     if stage == 1:
         utt2spk = kaldi_io.read_table(os.path.join(args.dir, "utt2spk"))
@@ -241,6 +257,9 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         torch.cuda.synchronize()
         t_loop = time.perf_counter() - t_loop
         t0 = time.perf_counter()
+        if warm is not None:
+            warm.join()
+        t_warm = time.perf_counter() - t0
         full = D.gather_stage1(index, emb, len(keys))
         D.reduce_speakers(ssum, scnt)
         mean = eng.speaker_mean(ssum, scnt)
@@ -249,8 +268,9 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         t0 = time.perf_counter()
         if rank == 0:
             full_h, mean_h = full.cpu().numpy(), mean.cpu().numpy()          # one device-to-host copy each
-            kaldi_io.save_atomic(kaldi_io.embeddings_to_dict(keys, full_h), os.path.join(args.dir, "utt2embedding.pt"))
-            kaldi_io.save_atomic(kaldi_io.speaker_dict(spk_names, mean_h), os.path.join(args.dir, "spk2embedding.pt"))
+            # same files as torch.save(dict of lists), written from the arrays (kaldi_io.save_embeddings_atomic)
+            kaldi_io.save_embeddings_atomic(keys, full_h, os.path.join(args.dir, "utt2embedding.pt"))
+            kaldi_io.save_embeddings_atomic(spk_names, mean_h, os.path.join(args.dir, "spk2embedding.pt"))
             if os.environ.get("FY_SIDECAR", "1") != "0":      # compact copies for the Arrow stage-3 fast path
                 parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.EMB_SIDECAR), keys, full_h)
                 parquet_pack.write_embedding_sidecar(os.path.join(args.dir, parquet_pack.SPK_SIDECAR), spk_names, mean_h)
@@ -271,13 +291,16 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         torch.cuda.synchronize()
         t_loop = time.perf_counter() - t_loop
         t0 = time.perf_counter()
+        if warm is not None:
+            warm.join()
+        t_warm = time.perf_counter() - t0
         full_cnt, flat = D.gather_stage2(index, counts, toks, len(keys))
         torch.cuda.synchronize()
         t_gather = time.perf_counter() - t0
         t0 = time.perf_counter()
         if rank == 0:
             cnt_h, flat_h = full_cnt.cpu().numpy(), flat.cpu().numpy()       # one device-to-host copy each
-            kaldi_io.save_atomic(dict(zip(keys, split_tokens(flat_h, cnt_h))), os.path.join(args.dir, "utt2speech_token.pt"))
+            kaldi_io.save_tokens_atomic(keys, flat_h, cnt_h, os.path.join(args.dir, "utt2speech_token.pt"))
             if os.environ.get("FY_SIDECAR", "1") != "0":
                 parquet_pack.write_token_sidecar_flat(os.path.join(args.dir, parquet_pack.TOK_SIDECAR), keys, flat_h, cnt_h)
         t_save = time.perf_counter() - t0
@@ -289,7 +312,10 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
             "precision": eng.precision, "audio_hours_per_s": sum(dur) / 3600.0 / wall,
             # rank 0's view; decode+stage and GPU overlap inside loop_s (reader pool + upload ring run ahead of the kernels)
             "native_reader_utts": int(direct.sum()),
-            "split_s": {"engine_and_weights": t_weights, "header_scan": t_scan, "header_scan_exposed": t_scan_wait,
+            # before_worker = interpreter start + imports of this process; process_group = rendezvous (communicator
+            # built later by a side thread: communicator_wait is what of it was still exposed in front of the gather)
+            "split_s": {"before_worker": since_exec, "process_group": t_init, "communicator_wait": t_warm,
+                        "engine_and_weights": t_weights, "header_scan": t_scan, "header_scan_exposed": t_scan_wait,
                         "loop": t_loop,
                         "loop_decode_wait": tm["decode_wait_s"], "loop_pack_upload": ex.ring.pack_seconds,
                         "loop_gpu_busy": gpu_s, "gather": t_gather, "tolist_save": t_save}}) + "\n")

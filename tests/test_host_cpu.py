@@ -192,6 +192,43 @@ def test_outputs_have_the_reference_format(tmp_path):
     assert sorted(p.name for p in tmp_path.iterdir()) == ["utt2embedding.pt", "utt2speech_token.pt"]   # no temp left
 
 
+def test_array_direct_writers_produce_what_torch_save_would(tmp_path):
+    """save_embeddings_atomic / save_tokens_atomic (what the CLIs call at 10^5+ keys) lay the pickle out from the arrays;
+    torch.load (both modes) and plain pickle must return the very dict torch.save(dict of lists) round-trips to."""
+    import pickle
+    import zipfile
+    rng = np.random.default_rng(4)
+    n = 20_011                                               # several chunks, last one ragged
+    keys = [f"spk{i % 7:02d}_utt_{i:06d}" for i in range(n)]
+    keys[3] = "方言_0003"                                     # non-ASCII key: BINUNICODE length is in bytes
+    emb = rng.standard_normal((n, 192)).astype(np.float32)
+    emb[0, :4] = [np.float32(1e-40), -0.0, np.float32(3.4e38), np.float32(-1.17549435e-38)]
+    kaldi_io.save_embeddings_atomic(keys, emb, tmp_path / "utt2embedding.pt")
+    kaldi_io.save_atomic(kaldi_io.embeddings_to_dict(keys, emb), tmp_path / "ref_e.pt")
+    ref = torch.load(tmp_path / "ref_e.pt")
+    for kw in ({}, {"weights_only": False}, {"weights_only": True}):
+        got = torch.load(tmp_path / "utt2embedding.pt", **kw)
+        assert type(got) is dict and list(got) == keys and got == ref
+        assert type(got[keys[0]]) is list and type(got[keys[0]][0]) is float
+    assert np.array_equal(np.array(got[keys[0]], dtype=np.float32).view(np.int32), emb[0].view(np.int32))   # -0.0 too
+    counts = rng.integers(0, 300, n)
+    counts[[0, 5, n - 1]] = 0                                # > 30 s utterances: key kept, empty list
+    flat = rng.integers(0, 6561, int(counts.sum())).astype(np.int32)
+    flat[:3] = [0, 255, 256]
+    kaldi_io.save_tokens_atomic(keys, flat, counts, tmp_path / "utt2speech_token.pt")
+    ref_t = dict(zip(keys, (flat[o - c:o].tolist() for o, c in zip(np.cumsum(counts), counts))))
+    for kw in ({}, {"weights_only": False}):
+        got = torch.load(tmp_path / "utt2speech_token.pt", **kw)
+        assert list(got) == keys and got == ref_t and got[keys[0]] == [] and type(got[keys[1]][0]) is int
+    with zipfile.ZipFile(tmp_path / "utt2speech_token.pt") as z:
+        assert pickle.loads(z.read("utt2speech_token/data.pkl")) == ref_t
+    kaldi_io.save_embeddings_atomic([], np.zeros((0, 192), np.float32), tmp_path / "empty.pt")
+    assert torch.load(tmp_path / "empty.pt") == {}
+    with pytest.raises(ValueError):
+        kaldi_io.save_tokens_atomic(["a"], np.array([70000]), np.array([1]), tmp_path / "bad.pt")
+    assert not any(p.name.startswith(".") for p in tmp_path.iterdir())                      # no temp left
+
+
 def test_save_atomic_leaves_nothing_on_failure(tmp_path):
     class Unpicklable:
         def __reduce__(self):
