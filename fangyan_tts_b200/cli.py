@@ -149,9 +149,7 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
 
         def _warm():
             torch.cuda.set_device(local_rank)
-            t = torch.zeros(1, device=torch.device("cuda", local_rank))
-            torch.distributed.all_reduce(t)
-            torch.cuda.synchronize()
+            D.warm_up(torch.device("cuda", local_rank))
 
         warm = threading.Thread(target=_warm, daemon=True)
         warm.start()
@@ -320,10 +318,13 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
                         "loop_decode_wait": tm["decode_wait_s"], "loop_pack_upload": ex.ring.pack_seconds,
                         "loop_gpu_busy": gpu_s, "gather": t_gather, "tolist_save": t_save}}) + "\n")
     pool.shutdown()
-    eng.close()
     if world > 1:
         import torch.distributed as dist
-        dist.barrier()
+        dist.barrier()                      # rank 0 has every row (and has written the files) before anybody leaves
+    if _FAST_EXIT:
+        return                              # run_tool ends the process right away: the driver reclaims GPU state
+    eng.close()
+    if world > 1:
         dist.destroy_process_group()
 
 
@@ -402,6 +403,26 @@ def _run_ranks(stage: int, args, world: int, prog: str) -> int:
     for k in kids:
         rc = rc or k.wait()
     return 1 if rc else 0
+
+
+_FAST_EXIT = False
+
+
+def run_tool(main) -> None:
+    """Entry of the tools/*.py scripts: run `main`, then leave with os._exit once the outputs are on disk.  Orderly
+    teardown of torch + the CUDA context + the NCCL communicator costs 2-3 s per process (profiles/r02_cli_e2e_n1.json:
+    process wall - in-process wall), i.e. more than stage 1 of a 100-hour job needs on the GPU; nothing is left to flush
+    or release that the operating system and the driver do not reclaim at exit.  FY_FAST_EXIT=0 restores sys.exit.
+    Errors still surface the ordinary way (traceback, status 1)."""
+    global _FAST_EXIT
+    _FAST_EXIT = os.environ.get("FY_FAST_EXIT", "1") != "0"
+    rc = main()
+    if not _FAST_EXIT:
+        sys.exit(rc)
+    logging.shutdown()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(int(rc or 0))
 
 
 def main_embedding(argv=None) -> int:

@@ -87,6 +87,19 @@ def gather_rows(tensors: List[torch.Tensor], counts: Optional[List[List[int]]] =
     return outs if r == dst else None
 
 
+def warm_up(device: torch.device) -> None:
+    """Build everything the result exchange will need, ahead of time: the communicator (first collective) and the
+    point-to-point connections of every rank to rank 0 (first send / receive per peer; ~1.4 s at 8 ranks when it happens
+    in front of the real gather).  The CLIs call this from a side thread under the extraction loop."""
+    if world() == 1:
+        return
+    t = torch.zeros(1, device=device)
+    dist.all_reduce(t)
+    gather_rows([torch.full((1, 8), rank(), dtype=torch.uint8, device=device)], [[1] * world()])
+    if device.type == "cuda":
+        torch.cuda.synchronize(device)
+
+
 def gather_stage1(index: torch.Tensor, emb: torch.Tensor, n_total: int,
                   rows: Optional[List[int]] = None) -> Optional[torch.Tensor]:
     """index [n_r] int64 (positions in wav.scp order), emb [n_r, 192] -> on rank 0 [n_total, 192] in wav.scp order;

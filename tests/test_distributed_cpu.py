@@ -25,6 +25,7 @@ def _fake_results(n):
 def _worker(rank, world, port, out_path):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     D.init(rank, world, backend="gloo", port=port)
+    D.warm_up(torch.device("cpu"))                                       # communicator + peer connections, as the CLIs do
     dur, emb, counts, toks, spk = _fake_results(N)
     mine = shard_indices(dur, rank, world)
     idx = torch.tensor(mine, dtype=torch.int64)

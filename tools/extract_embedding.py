@@ -5,7 +5,7 @@ from pathlib import Path
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 
-from fangyan_tts_b200.cli import main_embedding  # noqa: E402
+from fangyan_tts_b200.cli import main_embedding, run_tool  # noqa: E402
 
 if __name__ == "__main__":
-    sys.exit(main_embedding())
+    run_tool(main_embedding)

@@ -5,7 +5,7 @@ from pathlib import Path
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 
-from fangyan_tts_b200.cli import main_speech_token  # noqa: E402
+from fangyan_tts_b200.cli import main_speech_token, run_tool  # noqa: E402
 
 if __name__ == "__main__":
-    sys.exit(main_speech_token())
+    run_tool(main_speech_token)
