@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(256) cam_ctx_gate_kernel(const __half* __restr
   for (int s = 0; s < nseg; ++s) {
     const int t0 = s * seg_len, t1 = min(T, t0 + seg_len);
     float ax = 0.f, ay = 0.f;
-#pragma unroll 4
+#pragma unroll 8                                   // eight independent loads in flight; the adds stay in row order
     for (int t = t0 + rg; t < t1; t += 4) {
       const float2 v = __half22float2(hp[(size_t)t * 64]);
       ax += v.x; ay += v.y;
@@ -253,9 +253,11 @@ __global__ void __launch_bounds__(512) stats_kernel(const __half* __restrict__ x
   const int B = utt_B[u], T = utt_T[u];
   const float s = scale[c], b = shift[c];
   float sum = 0.f;
+#pragma unroll 8
   for (int t = 0; t < T; ++t) sum += fmaxf(__half2float(x[(size_t)(B + t) * ldx + c]) * s + b, 0.f);
   const float mean = sum / (float)T;
   float ss = 0.f;
+#pragma unroll 8
   for (int t = 0; t < T; ++t) {
     const float d = fmaxf(__half2float(x[(size_t)(B + t) * ldx + c]) * s + b, 0.f) - mean;
     ss += d * d;
