@@ -317,9 +317,10 @@ def frontend_figures(eng, hbm, batch=1024):
     gbs = 160000.0 * secs / (ms * 1e-3) / 1e9
     out["resample_24k_16k"] = {"ms": ms, "alg_bytes_per_audio_s": 160000.0, "achieved_GBps": gbs, "frac_of_hbm_peak": gbs / hbm,
                                "audio_hours_per_s": secs / 3600.0 / (ms * 1e-3), "l2": "1 GB in + 0.66 GB out per call"}
-    out["bound_note"] = ("fbank / log-mel are fp32-issue bound, not HBM bound: one 512-point real FFT + window + mel + log is ~1.1 M "
-                         "instructions per audio-second against 64 KB, so 30 % of the HBM peak would need ~94 % of the SM's fp32 "
-                         "issue rate; see DESIGN.md section 4.4")
+    out["bound_note"] = ("fbank / log-mel are instruction bound, not HBM bound (profiles/r02_ncu_frontend.md): fbank2 moves exactly its "
+                         "algorithmic bytes (4.4 % of the DRAM peak) but executes 1.1 G warp instructions per 1,024 x 10 s, which at a "
+                         "perfect issue rate is 0.98 ms = 10 % of the HBM peak; it reaches 55 % of that (shared-memory bank conflicts in "
+                         "the sparse mel gather are ~30 % of the kernel); see DESIGN.md section 4.4")
     return out
 
 

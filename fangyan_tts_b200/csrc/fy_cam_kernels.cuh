@@ -174,18 +174,21 @@ __global__ void __launch_bounds__(128) cam_gate_kernel(const float* __restrict__
 }
 
 // CAM gate in ONE launch per dense layer (replaces cam_segsum_kernel + cam_gate_kernel): one block of 256 threads per
-// utterance.  Phase 1: segment sums of h with coalesced half2 loads (thread = column pair x one of four row groups),
-// kept in shared memory together with the utterance total.  Phase 2: for every segment, ctx = utterance mean + segment
-// mean, gate = sigmoid(W2 relu(W1 ctx + b1) + b2).  An utterance is handled by one block whatever the batch holds, so
-// the gates do not depend on the batch composition.  kMaxSeg segments fit the shared buffer (a 64 s clip at seg_len
-// 100); longer utterances take the two-kernel path.
+// utterance.  Phase 1: segment sums of h; a thread = one column pair x one of four row groups, the four row groups
+// of a column pair are the four lanes of a quad, so their partial sums meet by two shuffles -- no shared memory and no
+// block barrier inside the segment loop, and the loads of consecutive segments overlap (the block is pure latency:
+// ~1,300 instructions per warp; with a barrier pair per segment it lived 45 k clk, profiles/r02_ncu_small_kernels.md).
+// Phase 2: for every segment, ctx = utterance mean + segment mean, gate = sigmoid(W2 relu(W1 ctx + b1) + b2), the two
+// dot products unrolled so that their weight loads are in flight together.  Summation orders are those of the
+// two-kernel path ((p0 + p1) + (p2 + p3) per segment, segments in order), and an utterance is handled by one block
+// whatever the batch holds, so the gates do not depend on the batch composition.  kGateMaxSeg segments fit the shared
+// buffer (a 64 s clip at seg_len 100); longer utterances take the two-kernel path.
 constexpr int kGateMaxSeg = 32;
 __global__ void __launch_bounds__(256) cam_ctx_gate_kernel(const __half* __restrict__ h, const int* __restrict__ utt_B,
                                                            const int* __restrict__ utt_T, const int* __restrict__ seg_base,
                                                            int seg_len, const float* __restrict__ w1, const float* __restrict__ b1,
                                                            const float* __restrict__ w2, const float* __restrict__ b2,
                                                            float* __restrict__ gate) {
-  __shared__ float part[4][128];
   __shared__ float ssum[kGateMaxSeg][128];
   __shared__ float total[128];
   __shared__ float ctx[2][128];
@@ -193,7 +196,7 @@ __global__ void __launch_bounds__(256) cam_ctx_gate_kernel(const __half* __restr
   const int u = blockIdx.x, tid = threadIdx.x;
   const int B = utt_B[u], T = utt_T[u], sb = seg_base[u];
   const int nseg = (T + seg_len - 1) / seg_len;
-  const int cp = tid & 63, rg = tid >> 6;          // column pair, row group
+  const int cp = tid >> 2, rg = tid & 3;           // column pair, row group (the four lanes of a quad)
   const __half2* hp = reinterpret_cast<const __half2*>(h) + (size_t)B * 64 + cp;
   float tx = 0.f, ty = 0.f;
   for (int s = 0; s < nseg; ++s) {
@@ -204,16 +207,12 @@ __global__ void __launch_bounds__(256) cam_ctx_gate_kernel(const __half* __restr
       const float2 v = __half22float2(hp[(size_t)t * 64]);
       ax += v.x; ay += v.y;
     }
-    part[rg][2 * cp] = ax; part[rg][2 * cp + 1] = ay;
-    __syncthreads();
-    if (tid < 128) {
-      const float v = (part[0][tid] + part[1][tid]) + (part[2][tid] + part[3][tid]);
-      ssum[s][tid] = v;
-      if (tid & 1) ty += v; else tx += v;
-    }
-    __syncthreads();
+    ax += __shfl_xor_sync(0xffffffffu, ax, 1); ay += __shfl_xor_sync(0xffffffffu, ay, 1);   // p0 + p1 | p2 + p3
+    ax += __shfl_xor_sync(0xffffffffu, ax, 2); ay += __shfl_xor_sync(0xffffffffu, ay, 2);   // (p0 + p1) + (p2 + p3)
+    if (rg == 0) { ssum[s][2 * cp] = ax; ssum[s][2 * cp + 1] = ay; }
+    tx += ax; ty += ay;
   }
-  if (tid < 128) total[tid] = (tid & 1) ? ty : tx;
+  if (rg == 0) { total[2 * cp] = tx; total[2 * cp + 1] = ty; }
   __syncthreads();
   // two segments per pass: threads [0, 128) take segment s, [128, 256) segment s + 1
   const int half = tid >> 7, c = tid & 127;
@@ -228,6 +227,7 @@ __global__ void __launch_bounds__(256) cam_ctx_gate_kernel(const __half* __restr
     if (on) {   // 64 outputs x 128 inputs: two threads per output, combined by shuffle
       const int o = c >> 1, hf = c & 1;
       float a = 0.f;
+#pragma unroll 16
       for (int k = hf * 64; k < hf * 64 + 64; ++k) a += w1[k * 64 + o] * ctx[half][k];
       a += __shfl_xor_sync(0xffffffffu, a, 1);
       if (hf == 0) hid[half][o] = fmaxf(a + b1[o], 0.f);
@@ -235,6 +235,7 @@ __global__ void __launch_bounds__(256) cam_ctx_gate_kernel(const __half* __restr
     __syncthreads();
     if (on && c < 32) {
       float a = b2[c];
+#pragma unroll 16
       for (int k = 0; k < 64; ++k) a += w2[k * 32 + c] * hid[half][k];
       gate[(size_t)(sb + s) * 32 + c] = 1.0f / (1.0f + expf(-a));
     }
