@@ -173,70 +173,103 @@ __global__ void __launch_bounds__(128) cam_gate_kernel(const float* __restrict__
   }
 }
 
-// CAM gate in ONE launch per dense layer (replaces cam_segsum_kernel + cam_gate_kernel): one block of 256 threads per
-// utterance.  Phase 1: segment sums of h; a thread = one column pair x one of four row groups, the four row groups
-// of a column pair are the four lanes of a quad, so their partial sums meet by two shuffles -- no shared memory and no
-// block barrier inside the segment loop, and the loads of consecutive segments overlap (the block is pure latency:
-// ~1,300 instructions per warp; with a barrier pair per segment it lived 45 k clk, profiles/r02_ncu_small_kernels.md).
-// Phase 2: for every segment, ctx = utterance mean + segment mean, gate = sigmoid(W2 relu(W1 ctx + b1) + b2), the two
-// dot products unrolled so that their weight loads are in flight together.  Summation orders are those of the
-// two-kernel path ((p0 + p1) + (p2 + p3) per segment, segments in order), and an utterance is handled by one block
-// whatever the batch holds, so the gates do not depend on the batch composition.  kGateMaxSeg segments fit the shared
-// buffer (a 64 s clip at seg_len 100); longer utterances take the two-kernel path.
-constexpr int kGateMaxSeg = 32;
-__global__ void __launch_bounds__(256) cam_ctx_gate_kernel(const __half* __restrict__ h, const int* __restrict__ utt_B,
-                                                           const int* __restrict__ utt_T, const int* __restrict__ seg_base,
-                                                           int seg_len, const float* __restrict__ w1, const float* __restrict__ b1,
-                                                           const float* __restrict__ w2, const float* __restrict__ b2,
-                                                           float* __restrict__ gate) {
+// CAM gate in ONE launch per dense layer (replaces cam_segsum_kernel + cam_gate_kernel): one block of 512 threads per
+// utterance.  The block is pure latency (~1,300 instructions per warp, profiles/r02_ncu_small_kernels.md), so the design
+// is about how many dependent round trips to memory it makes:
+//   * W1 (32 KB) is requested first and parked in registers, then stored to shared memory after phase 1: its latency
+//     hides under the segment sums and phase 2 never waits for global memory on it;
+//   * phase 1, segment sums of h: a thread = one column pair x one of EIGHT row groups, the eight row groups of a column
+//     pair are neighbouring lanes, so their partial sums meet by three shuffles -- no shared memory, no block barrier in
+//     the segment loop, one batch of <= 16 loads per 100-frame segment;
+//   * phase 2, for every segment ctx = utterance mean + segment mean, gate = sigmoid(W2 relu(W1 ctx + b1) + b2): four
+//     segments per pass (128 threads each), i.e. one pass for clips up to 8 s.
+// An utterance is handled by one block whatever the batch holds and every sum has a fixed order, so the gates do not
+// depend on the batch composition.  kGateMaxSeg segments fit the shared buffer (a 32 s clip at seg_len 100); longer
+// utterances take the two-kernel path.  __launch_bounds__(512, 2): without the second number ptxas squeezes the kernel
+// into 40 registers and, to get there, issues every load right in front of its use (sixteen serial round trips per
+// segment instead of one batch -- visible in the SASS); 64 registers keep two blocks per SM, one wave for <= 296 clips.
+constexpr int kGateMaxSeg = 16;
+constexpr int kGateThreads = 512;
+constexpr int kGateBatch = 16;                    // rows a thread requests at a time in phase 1
+__global__ void __launch_bounds__(kGateThreads, 2) cam_ctx_gate_kernel(const __half* __restrict__ h, const int* __restrict__ utt_B,
+                                                                    const int* __restrict__ utt_T, const int* __restrict__ seg_base,
+                                                                    int seg_len, const float* __restrict__ w1, const float* __restrict__ b1,
+                                                                    const float* __restrict__ w2, const float* __restrict__ b2,
+                                                                    float* __restrict__ gate) {
   __shared__ float ssum[kGateMaxSeg][128];
   __shared__ float total[128];
-  __shared__ float ctx[2][128];
-  __shared__ float hid[2][64];
+  __shared__ float ctx[4][128];
+  __shared__ float hid[4][64];
+  __shared__ float4 sw1[128 * 64 / 4];             // W1 [128 inputs][64 outputs]
   const int u = blockIdx.x, tid = threadIdx.x;
+  float4 wreg[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) wreg[i] = __ldg(reinterpret_cast<const float4*>(w1) + tid + kGateThreads * i);
   const int B = utt_B[u], T = utt_T[u], sb = seg_base[u];
   const int nseg = (T + seg_len - 1) / seg_len;
-  const int cp = tid >> 2, rg = tid & 3;           // column pair, row group (the four lanes of a quad)
+  const int cp = tid >> 3, rg = tid & 7;           // column pair, row group (eight neighbouring lanes)
+  const int grp = tid >> 7, c = tid & 127;         // phase 2: segment of the pass, channel
+  const float b1v = __ldg(b1 + (c >> 1)), b2v = __ldg(b2 + (c & 31));
   const __half2* hp = reinterpret_cast<const __half2*>(h) + (size_t)B * 64 + cp;
   float tx = 0.f, ty = 0.f;
   for (int s = 0; s < nseg; ++s) {
     const int t0 = s * seg_len, t1 = min(T, t0 + seg_len);
     float ax = 0.f, ay = 0.f;
-#pragma unroll 8                                   // eight independent loads in flight; the adds stay in row order
-    for (int t = t0 + rg; t < t1; t += 4) {
-      const float2 v = __half22float2(hp[(size_t)t * 64]);
-      ax += v.x; ay += v.y;
+    // kGateBatch predicated loads at a time (a fixed trip count: a `#pragma unroll` of the plain row loop leaves short
+    // trip counts to a serial remainder loop, one round trip per row); rows beyond the segment add exact zeros
+    for (int base = t0 + rg; base < t1; base += 8 * kGateBatch) {
+      __half2 v[kGateBatch];
+#pragma unroll
+      for (int i = 0; i < kGateBatch; ++i)        // unconditional loads (row index clamped into the segment) ...
+        v[i] = __ldg(hp + (size_t)min(base + 8 * i, t1 - 1) * 64);
+#pragma unroll
+      for (int i = 0; i < kGateBatch; ++i) {      // ... masked when they are added
+        const float2 f = __half22float2(v[i]);
+        const bool in = base + 8 * i < t1;
+        ax += in ? f.x : 0.f; ay += in ? f.y : 0.f;
+      }
     }
-    ax += __shfl_xor_sync(0xffffffffu, ax, 1); ay += __shfl_xor_sync(0xffffffffu, ay, 1);   // p0 + p1 | p2 + p3
-    ax += __shfl_xor_sync(0xffffffffu, ax, 2); ay += __shfl_xor_sync(0xffffffffu, ay, 2);   // (p0 + p1) + (p2 + p3)
+#pragma unroll
+    for (int m = 1; m < 8; m <<= 1) {
+      ax += __shfl_xor_sync(0xffffffffu, ax, m);
+      ay += __shfl_xor_sync(0xffffffffu, ay, m);
+    }
     if (rg == 0) { ssum[s][2 * cp] = ax; ssum[s][2 * cp + 1] = ay; }
     tx += ax; ty += ay;
   }
   if (rg == 0) { total[2 * cp] = tx; total[2 * cp + 1] = ty; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) sw1[tid + kGateThreads * i] = wreg[i];
   __syncthreads();
-  // two segments per pass: threads [0, 128) take segment s, [128, 256) segment s + 1
-  const int half = tid >> 7, c = tid & 127;
-  for (int s0 = 0; s0 < nseg; s0 += 2) {
-    const int s = s0 + half;
+  const float* w1s = reinterpret_cast<const float*>(sw1);
+  // four segments per pass: threads [128 g, 128 g + 128) take segment s0 + g
+  for (int s0 = 0; s0 < nseg; s0 += 4) {
+    const int s = s0 + grp;
     const bool on = s < nseg;
     if (on) {
       const int n = min(T, (s + 1) * seg_len) - s * seg_len;
-      ctx[half][c] = total[c] / (float)T + ssum[s][c] / (float)n;
+      ctx[grp][c] = total[c] / (float)T + ssum[s][c] / (float)n;
     }
     __syncthreads();
     if (on) {   // 64 outputs x 128 inputs: two threads per output, combined by shuffle
       const int o = c >> 1, hf = c & 1;
       float a = 0.f;
 #pragma unroll 16
-      for (int k = hf * 64; k < hf * 64 + 64; ++k) a += w1[k * 64 + o] * ctx[half][k];
+      for (int k = hf * 64; k < hf * 64 + 64; ++k) a += w1s[k * 64 + o] * ctx[grp][k];
       a += __shfl_xor_sync(0xffffffffu, a, 1);
-      if (hf == 0) hid[half][o] = fmaxf(a + b1[o], 0.f);
+      if (hf == 0) hid[grp][o] = fmaxf(a + b1v, 0.f);
     }
     __syncthreads();
     if (on && c < 32) {
-      float a = b2[c];
-#pragma unroll 16
-      for (int k = 0; k < 64; ++k) a += w2[k * 32 + c] * hid[half][k];
+      float a = b2v;
+#pragma unroll
+      for (int k0 = 0; k0 < 64; k0 += 16) {     // sixteen weight loads in flight, then their FMAs in order
+        float wv[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) wv[i] = __ldg(w2 + (k0 + i) * 32 + c);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a += wv[i] * hid[grp][k0 + i];
+      }
       gate[(size_t)(sb + s) * 32 + c] = 1.0f / (1.0f + expf(-a));
     }
     __syncthreads();

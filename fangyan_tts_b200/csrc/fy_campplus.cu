@@ -481,7 +481,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
       }
       if (fused_gate) {
         c->launches += 1;  // cam_ctx_gate
-        camk::cam_ctx_gate_kernel<<<n_utts, 256, 0, st>>>(hb, d_B, d_T2, d_segbase, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
+        camk::cam_ctx_gate_kernel<<<n_utts, camk::kGateThreads, 0, st>>>(hb, d_B, d_T2, d_segbase, cf.seg_len, d.cw1, d.cb1, d.cw2, d.cb2, gate);
       } else {
         c->launches += 2;  // cam_segsum, cam_gate
         camk::cam_segsum_kernel<<<nseg, 128, 0, st>>>(hb, d_B, d_T2, d_segbase, d_segutt, cf.seg_len, segsum);
