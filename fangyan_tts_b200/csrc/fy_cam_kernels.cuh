@@ -19,49 +19,66 @@ __device__ __forceinline__ float2 unpack2(uint32_t u) { return __half22float2(*r
 // Stem: Conv2d(1, 32, 3x3, pad 1) + BN + ReLU over (freq, time).  feat is packed [frames, 80] fp32.
 // out: [R100, 82, 32] fp16 channels-last with zero columns at p = 0 and p = 81 (zero_pads_kernel) and zero guard rows.
 // rowsrc[r] = feat row of time row r or -1 for guard rows.  w: [32][3 (freq)][3 (time)].
-// grid = R100, block = 320 (80 freq x 4 groups of 8 channels).
-__global__ void __launch_bounds__(320) stem_kernel(const float* __restrict__ feat, const int* __restrict__ rowsrc,
-                                                   int R100, const float* __restrict__ w,
-                                                   const float* __restrict__ scale, const float* __restrict__ shift,
-                                                   __half* __restrict__ out) {
-  const int r = blockIdx.x;
-  const int src = rowsrc[r];
-  if (src < 0) {   // guard row: explicit zeros (the workspace is not cleared; the pad slots come from zero_pads_kernel)
-    *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + threadIdx.x % 80 + 1) * 32 + (threadIdx.x / 80) * 8) =
-        make_uint4(0u, 0u, 0u, 0u);
-    return;
-  }
-  __shared__ float in[3][82];
+// One block = kStemRows consecutive time rows, 320 threads (80 freq x 4 groups of 8 channels): the rows' sources, the
+// kStemRows + 2 input rows and the 288 weights are fetched once per block (one block per row spent its life on three
+// dependent round trips for 100 instructions of work, profiles/r02_ncu_small_kernels.md) and a thread keeps its
+// 8 x 9 weights in registers across the rows.  grid = ceil(R100 / kStemRows).
+constexpr int kStemRows = 8;
+__global__ void __launch_bounds__(320, 2) stem_kernel(const float* __restrict__ feat, const int* __restrict__ rowsrc,
+                                                      int R100, const float* __restrict__ w,
+                                                      const float* __restrict__ scale, const float* __restrict__ shift,
+                                                      __half* __restrict__ out) {
+  __shared__ int srow[kStemRows + 2];
+  __shared__ float in[kStemRows + 2][82];
   __shared__ float sw[32 * 9 + 64];
+  const int r0 = blockIdx.x * kStemRows;
+  if (threadIdx.x < kStemRows + 2) {
+    const int rr = r0 + (int)threadIdx.x - 1;
+    srow[threadIdx.x] = (rr >= 0 && rr < R100) ? rowsrc[rr] : -1;
+  }
   for (int i = threadIdx.x; i < 32 * 9; i += 320) sw[i] = w[i];
   for (int i = threadIdx.x; i < 64; i += 320) sw[288 + i] = i < 32 ? scale[i] : shift[i - 32];
-  for (int i = threadIdx.x; i < 3 * 82; i += 320) {
+  __syncthreads();
+  for (int i = threadIdx.x; i < (kStemRows + 2) * 82; i += 320) {
     const int j = i / 82, p = i % 82;
-    const int rr = r + j - 1;
-    const int s = (rr >= 0 && rr < R100) ? rowsrc[rr] : -1;
+    const int s = srow[j];
     in[j][p] = (s >= 0 && p >= 1 && p <= 80) ? feat[(size_t)s * 80 + p - 1] : 0.f;
   }
   __syncthreads();
   const int f = threadIdx.x % 80, cg = threadIdx.x / 80;
-  float x[3][3];  // [freq i][time j]
+  float wr[8][9];
 #pragma unroll
-  for (int i = 0; i < 3; ++i)
+  for (int k = 0; k < 8; ++k)
 #pragma unroll
-    for (int j = 0; j < 3; ++j) x[i][j] = in[j][f + i];
-  float y[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const int c = cg * 8 + k;
-    float a = 0.f;
+    for (int q = 0; q < 9; ++q) wr[k][q] = sw[(cg * 8 + k) * 9 + q];
+#pragma unroll 1
+  for (int t = 0; t < kStemRows; ++t) {
+    const int r = r0 + t;
+    if (r >= R100) break;
+    __half* dst = out + ((size_t)r * 82 + f + 1) * 32 + cg * 8;
+    if (srow[t + 1] < 0) {   // guard row: explicit zeros (the workspace is not cleared; the pad slots come from zero_pads_kernel)
+      *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+      continue;
+    }
+    float x[3][3];  // [freq i][time j]
 #pragma unroll
     for (int i = 0; i < 3; ++i)
 #pragma unroll
-      for (int j = 0; j < 3; ++j) a += sw[c * 9 + i * 3 + j] * x[i][j];
-    y[k] = fmaxf(a * sw[288 + c] + sw[320 + c], 0.f);
+      for (int j = 0; j < 3; ++j) x[i][j] = in[t + j][f + i];
+    float y[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float a = 0.f;
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) a += wr[k][i * 3 + j] * x[i][j];
+      y[k] = fmaxf(a * sw[288 + cg * 8 + k] + sw[320 + cg * 8 + k], 0.f);
+    }
+    uint4 o;
+    o.x = pack2(y[0], y[1]); o.y = pack2(y[2], y[3]); o.z = pack2(y[4], y[5]); o.w = pack2(y[6], y[7]);
+    *reinterpret_cast<uint4*>(dst) = o;
   }
-  uint4 o;
-  o.x = pack2(y[0], y[1]); o.y = pack2(y[2], y[3]); o.z = pack2(y[4], y[5]); o.w = pack2(y[6], y[7]);
-  *reinterpret_cast<uint4*>(out + ((size_t)r * 82 + f + 1) * 32 + cg * 8) = o;
 }
 
 // The FCM activation buffers [R100][fp slots][32 ch] fp16 keep one zero pad slot at each end of every time row (the

@@ -408,7 +408,7 @@ extern "C" int fy_campplus_forward(fy_ctx* ctx, const float* feat, const int32_t
       camk::pos_mask_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_rowsrc, R100, Q, lo, hi, m);
     };
     mk(41, 0, 39, m42s); mk(42, 1, 40, m42); mk(21, 0, 19, m22s); mk(22, 1, 20, m22); mk(11, 0, 9, m11s);
-    camk::stem_kernel<<<R100, 320, 0, st>>>(feat, d_rowsrc, R100, p->stem_w, p->stem_bn.scale, p->stem_bn.shift, H(lay.o_x0));
+    camk::stem_kernel<<<(R100 + camk::kStemRows - 1) / camk::kStemRows, 320, 0, st>>>(feat, d_rowsrc, R100, p->stem_w, p->stem_bn.scale, p->stem_bn.shift, H(lay.o_x0));
     FY_CUDA(cudaGetLastError());
   }
   // ---- FCM residual stages
