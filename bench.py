@@ -339,15 +339,15 @@ def run_ours(args):
     t_start = time.perf_counter()
     watchdog = float(os.environ.get("FY_BENCH_WATCHDOG", "240"))
 
-    def mark(stage):
+    def mark(stage, extra_s=0.0):
         """One stderr line per phase and rank, and a watchdog: a phase that takes longer than FY_BENCH_WATCHDOG
-        seconds dumps every thread's stack and ends the process (a hung rank must not hold an 8-GPU box)."""
+        (+ extra_s) seconds dumps every thread's stack and ends the process (a hung rank must not hold an 8-GPU box)."""
         import faulthandler
         sys.stderr.write(f"[bench r{rank}/{world} +{time.perf_counter() - t_start:6.1f}s] {stage}\n")
         sys.stderr.flush()
         faulthandler.cancel_dump_traceback_later()
         if watchdog > 0 and stage != "done":
-            faulthandler.dump_traceback_later(watchdog, exit=True)
+            faulthandler.dump_traceback_later(watchdog + extra_s, exit=True)
 
     mark("start")
     torch.cuda.set_device(local)
@@ -443,14 +443,14 @@ def run_ours(args):
         return max_over_ranks(a.elapsed_time(b))
 
     warm = max(args.warmup, 3)
-    mark("shard resident")
+    mark("shard resident", extra_s=2.0 * warm)
     for k in range(warm):
         step_device()
         if k == 0:
             torch.cuda.synchronize()
             mark("first step (with the first exchange) done")
     torch.cuda.synchronize()
-    mark("warm-up done")
+    mark("warm-up done", extra_s=2.0 * args.steps)           # the timed region grows with --steps
     # ---- the exchange delivered exactly what the ranks computed (fingerprints of index x row bits, all-reduced)
     fp = torch.stack([D.checksum(gidx, last["emb"]), D.checksum_ragged(gidx, gcnt, last["tok"])])
     if world > 1:
@@ -526,7 +526,7 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    mark("process group closed")
+    mark("process group closed", extra_s=600.0)             # rank 0's CPU leg follows (oracle / literal reference stack)
     if rank != 0:
         mark("done")
         return 0
