@@ -1,5 +1,6 @@
 """CPU tests of the host side: batching / sharding policy, WAV decode (row A1), Kaldi tables, the .pt output
 contract (B1), the ONNX initialiser reader and the synthetic-weight tables."""
+import os
 import struct
 import subprocess
 import sys
@@ -311,3 +312,32 @@ def test_cli_fails_loudly_without_gpu_and_writes_nothing(tmp_path, tool):
     assert r.returncode != 0
     assert "no CUDA device" in r.stderr or "FyError" in r.stderr
     assert sorted(p.name for p in tmp_path.iterdir()) == before
+
+
+def test_run_tool_exit_paths(tmp_path):
+    """cli.run_tool (entry of the two tool scripts): status of `main` becomes the process status, buffered output is
+    flushed before os._exit, an exception still ends with a traceback and status 1, FY_FAST_EXIT=0 takes sys.exit."""
+    prog = ("import sys; sys.path.insert(0, %r)\n"
+            "from fangyan_tts_b200 import cli\n"
+            "def main():\n"
+            "    print('out-line'); sys.stderr.write('err-line\\n')\n"
+            "    if sys.argv[1] == 'raise': raise RuntimeError('boom')\n"
+            "    return int(sys.argv[1])\n"
+            "cli.run_tool(main)\n") % str(ROOT)
+    for env_extra in ({}, {"FY_FAST_EXIT": "0"}):
+        env = dict(os.environ, **env_extra)
+        ok = subprocess.run([sys.executable, "-c", prog, "0"], capture_output=True, text=True, env=env)
+        assert ok.returncode == 0 and "out-line" in ok.stdout and "err-line" in ok.stderr
+        bad = subprocess.run([sys.executable, "-c", prog, "3"], capture_output=True, text=True, env=env)
+        assert bad.returncode == 3 and "out-line" in bad.stdout
+        exc = subprocess.run([sys.executable, "-c", prog, "raise"], capture_output=True, text=True, env=env)
+        assert exc.returncode == 1 and "RuntimeError: boom" in exc.stderr
+
+
+def test_seconds_since_exec_is_this_process_age():
+    import time
+    from fangyan_tts_b200.cli import _seconds_since_exec
+    a = _seconds_since_exec()
+    time.sleep(0.3)
+    b = _seconds_since_exec()
+    assert 0.0 <= a < 3600.0 and 0.2 <= b - a <= 1.0
