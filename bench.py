@@ -60,6 +60,9 @@ def parse_args():
     ap.add_argument("--cli-e2e", type=int, default=0, metavar="N",
                     help="time the drop-in CLIs over N utterances: WAV files on tmpfs -> the three .pt files")
     ap.add_argument("--cli-files", type=int, default=4000, help="distinct WAV files behind the --cli-e2e keys")
+    ap.add_argument("--serialise", type=int, default=0, metavar="N",
+                    help="SURVEY 8(d) region (iii) alone, CPU only: N result rows (192-float embeddings, 75-250 token ids) -> "
+                         "the three .pt files, array-direct writers against tolist() + torch.save")
     ap.add_argument("--long-stress", action="store_true",
                     help="BASELINE configs[3]: 256 clips of 1-30 s (two at exactly 30.0 s), 12 layers, bf16x3 and bf16")
     return ap.parse_args()
@@ -719,6 +722,51 @@ def run_stage3_pack(args):
     return 0
 
 
+def run_serialise(args):
+    """SURVEY.md 8(d) region (iii), serialisation only (row A11): from the gathered result arrays on rank 0's host to
+    utt2embedding.pt / utt2speech_token.pt.  `value` = the array-direct writers the CLIs use (kaldi_io.save_*_atomic);
+    `cpu_baseline` = what the reference does at extract_embedding.py:41,57-58 / extract_speech_token.py:48,58: a
+    Python list per key (tolist) and torch.save of the dict.  Both outputs are loaded back and compared.  No GPU."""
+    import tempfile
+    import torch
+    from fangyan_tts_b200 import kaldi_io
+    from fangyan_tts_b200.pipeline import split_tokens
+    n = args.serialise
+    rng = np.random.default_rng(1986 + 6)
+    keys = [f"utt_{i:07d}" for i in range(n)]
+    emb = rng.standard_normal((n, 192)).astype(np.float32)
+    counts = rng.integers(75, 251, n)
+    flat = rng.integers(0, 6561, int(counts.sum())).astype(np.int32)
+    with tempfile.TemporaryDirectory() as tmp:
+        t0 = time.perf_counter()
+        kaldi_io.save_embeddings_atomic(keys, emb, os.path.join(tmp, "utt2embedding.pt"))
+        t_e = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        kaldi_io.save_tokens_atomic(keys, flat, counts, os.path.join(tmp, "utt2speech_token.pt"))
+        t_t = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        kaldi_io.save_atomic(kaldi_io.embeddings_to_dict(keys, emb), os.path.join(tmp, "ref_e.pt"))
+        r_e = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        kaldi_io.save_atomic(dict(zip(keys, split_tokens(flat, counts))), os.path.join(tmp, "ref_t.pt"))
+        r_t = time.perf_counter() - t0
+        sizes = {f: os.path.getsize(os.path.join(tmp, f)) for f in ("utt2embedding.pt", "utt2speech_token.pt", "ref_e.pt", "ref_t.pt")}
+        t0 = time.perf_counter()
+        same = (torch.load(os.path.join(tmp, "utt2embedding.pt")) == torch.load(os.path.join(tmp, "ref_e.pt")) and
+                torch.load(os.path.join(tmp, "utt2speech_token.pt")) == torch.load(os.path.join(tmp, "ref_t.pt")))
+        t_load = time.perf_counter() - t0
+    hours = n * 6.5 / 3600.0
+    print(json.dumps({
+        "metric": "serialise_rows_per_sec", "unit": "utterances/s", "utts": n, "approx_audio_hours": hours,
+        "value": n / (t_e + t_t), "seconds": {"utt2embedding.pt": t_e, "utt2speech_token.pt": t_t},
+        "cpu_baseline": {"kind": "port", "value": n / (r_e + r_t), "cores": 1,
+                         "seconds": {"utt2embedding.pt": r_e, "utt2speech_token.pt": r_t},
+                         "sample": "tolist() per key + torch.save(dict of lists), as the reference's loops do"},
+        "identical_after_torch_load": bool(same), "load_back_seconds": t_load, "bytes": sizes,
+        "host": {"cores": len(os.sched_getaffinity(0))}}), flush=True)
+    return 0 if same else 5
+
+
 def run_cli_e2e(args):
     """SURVEY.md 8(d) regions (ii) and (iii) through the shipped command lines: N keys over `--cli-files` distinct
     16 kHz PCM16 WAVs on tmpfs -> tools/extract_embedding.py, then tools/extract_speech_token.py (separate processes,
@@ -856,6 +904,8 @@ if __name__ == "__main__":
     a = parse_args()
     if a.stage3_pack:
         rc = run_stage3_pack(a)
+    elif a.serialise:
+        rc = run_serialise(a)
     elif a.frontend_sweep:
         rc = run_frontend_sweep(a)
     elif a.cli_e2e:
