@@ -82,6 +82,14 @@ class FsmnAttention(nn.Module):
         self.fsmn = nn.Conv1d(d, d, cfg.fsmn_kernel, groups=d, bias=False)
         self.pad = (cfg.fsmn_kernel - 1) // 2
 
+    def fsmn_memory(self, v, mask_pad):
+        """FSMN memory of the value projection: depthwise conv over time (zero padding, no bias) + identity, masked
+        before and after.  The same function as FunASR's SAN-M `forward_fsmn`, which S3Tokenizer's attention block
+        derives from; tests/test_oracle_pins_cpu.py checks it against the copy of that code shipped in vllm."""
+        vm = v * mask_pad
+        mem = self.fsmn(F.pad(vm.transpose(1, 2), (self.pad, self.pad))).transpose(1, 2)
+        return (mem + vm) * mask_pad
+
     def forward(self, x, mask_pad, bias, cos, sin):
         # x [B, T, d]; mask_pad [B, T, 1] (1 = valid); bias [B, 1, 1, T] additive
         b, t, d = x.shape
@@ -90,9 +98,7 @@ class FsmnAttention(nn.Module):
         k = self.key(x).view(b, t, h, dh)
         v = self.value(x).view(b, t, h, dh)
         q, k = apply_rope(q, cos, sin), apply_rope(k, cos, sin)
-        vm = v.reshape(b, t, d) * mask_pad
-        mem = self.fsmn(F.pad(vm.transpose(1, 2), (self.pad, self.pad))).transpose(1, 2)
-        mem = (mem + vm) * mask_pad
+        mem = self.fsmn_memory(v.reshape(b, t, d), mask_pad)
         scale = dh ** -0.25
         qk = (q.permute(0, 2, 1, 3) * scale) @ (k.permute(0, 2, 3, 1) * scale) + bias
         w = torch.softmax(qk.float(), dim=-1).to(q.dtype)
