@@ -25,7 +25,13 @@ def _fake_results(n):
 def _worker(rank, world, port, out_path):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     D.init(rank, world, backend="gloo", port=port)
-    D.warm_up(torch.device("cpu"))                                       # communicator + peer connections, as the CLIs do
+    # communicator + peer connections from a side thread while this thread keeps working, as the CLIs do
+    import threading
+    warm = threading.Thread(target=D.warm_up, args=(torch.device("cpu"),), daemon=True)
+    warm.start()
+    busy = sum(float((torch.randn(64, 64) @ torch.randn(64, 64)).sum()) for _ in range(50))
+    warm.join(timeout=120)
+    assert not warm.is_alive() and busy == busy
     dur, emb, counts, toks, spk = _fake_results(N)
     mine = shard_indices(dur, rank, world)
     idx = torch.tensor(mine, dtype=torch.int64)
