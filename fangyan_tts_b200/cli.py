@@ -148,8 +148,14 @@ def _worker(local_rank: int, world: int, stage: int, args, port: int, spawned: b
         import threading
 
         def _warm():
-            torch.cuda.set_device(local_rank)
-            D.warm_up(torch.device("cuda", local_rank))
+            try:
+                torch.cuda.set_device(local_rank)
+                D.warm_up(torch.device("cuda", local_rank))
+            except BaseException:       # a rank whose warm-up failed must not go on to the real exchange: its peers
+                import traceback        # would pair its sends with their warm-up receives.  End it; the launcher's
+                traceback.print_exc()   # watcher then ends every rank and nothing is written.
+                sys.stderr.flush()
+                os._exit(1)
 
         warm = threading.Thread(target=_warm, daemon=True)
         warm.start()
